@@ -1,0 +1,335 @@
+/*
+ * accel_ps.h — C ABI of the B200-native parameter-server (PS) step.
+ *
+ * This is the drop-in boundary for ONE path of gaocegege/kubeflow-controller's
+ * TFJobs: on each PS task, aggregate the gradients pushed by N workers for the
+ * task's variable shard and apply the optimizer update (SGD / Momentum / Adam).
+ * The reference has no FFI of its own (it is a Go control plane; the arithmetic
+ * lives in TensorFlow 1.4.0, pinned by image tag examples/tfjob/dist.yml:13,32),
+ * so every entry point below cites the reference interface or call site whose
+ * behaviour it reproduces. The Go package pkg/accel binds exactly these symbols
+ * through cgo.
+ *
+ * Conventions
+ *   - plain C types only; no exceptions cross the boundary;
+ *   - return value 0 = ACCEL_OK, negative = accel_status error code; the
+ *     message of the last error on the calling thread is accel_last_error();
+ *   - every `*_dev` / device pointer is CALLER-OWNED device memory, never freed
+ *     or retained past the call; state/gradient pointers must be 16-byte
+ *     aligned (32-byte for ACCEL_KERNEL_LDG256);
+ *   - `stream` is a cudaStream_t passed as an opaque pointer (NULL = the legacy
+ *     default stream); kernels are enqueued asynchronously on it;
+ *   - PS task_index i (pkg/tensorflow/distributed.go:151 "--task_index=%d")
+ *     <-> GPU ordinal gpu_ordinals[i] <-> collective rank i <-> shard i;
+ *   - calls on the same task must be serialised by the caller; different tasks
+ *     may be driven from different host threads (each call sets its device);
+ *   - there is NO CPU fallback: without a usable CUDA device every compute
+ *     entry point fails with ACCEL_ERR_CUDA.
+ */
+#ifndef ACCEL_PS_H_
+#define ACCEL_PS_H_
+
+#include <stddef.h>
+#include <stdint.h>
+
+#ifdef __cplusplus
+extern "C" {
+#endif
+
+#define ACCEL_PS_VERSION 10100 /* major*10000 + minor*100 + patch */
+#define ACCEL_MAX_WORKERS 64   /* gradients summed by one launch */
+#define ACCEL_MAX_PS 16        /* PS tasks (= GPUs of one box) per context */
+
+typedef struct accel_ctx accel_ctx;
+typedef void *accel_stream_t; /* cudaStream_t */
+
+typedef enum accel_status {
+  ACCEL_OK = 0,
+  ACCEL_ERR_INVALID = -1, /* bad argument (NULL, out of range, unknown enum) */
+  ACCEL_ERR_ALIGN = -2,   /* pointer not aligned for the vector path */
+  ACCEL_ERR_CUDA = -3,    /* CUDA runtime error (message has the detail) */
+  ACCEL_ERR_NOMEM = -4,   /* allocation failed */
+  ACCEL_ERR_BUFSIZE = -5, /* caller's output buffer too small */
+  ACCEL_ERR_STATE = -6    /* call not valid in the context's current state */
+} accel_status;
+
+typedef enum accel_dtype { ACCEL_F32 = 0, ACCEL_BF16 = 1 } accel_dtype;
+
+/* How the N worker gradients become one gradient.
+ * SUM  : g = ((g0 + g1) + g2) + ...  in worker-index order, fp32.
+ * MEAN : the SUM divided by float(N) — what TF-1.4's ConditionalAccumulator
+ *        take_grad returns under SyncReplicasOptimizer
+ *        (examples/workdir/mnist_replica.py:172-182). */
+typedef enum accel_aggregate { ACCEL_AGG_SUM = 0, ACCEL_AGG_MEAN = 1 } accel_aggregate;
+
+typedef enum accel_optimizer {
+  ACCEL_OPT_SGD = 0,      /* tf.train.GradientDescentOptimizer, examples/workdir/mnist_softmax.py:59 */
+  ACCEL_OPT_MOMENTUM = 1, /* tf.train.MomentumOptimizer (BASELINE config 3) */
+  ACCEL_OPT_ADAM = 2      /* tf.train.AdamOptimizer, examples/workdir/mnist_replica.py:170 */
+} accel_optimizer;
+
+/* Kernel variant: an explicit choice of the caller (benchmarks sweep it), never
+ * a dispatch on hardware. AUTO = the variant measured fastest on B200. */
+typedef enum accel_kernel {
+  ACCEL_KERNEL_AUTO = 0,
+  ACCEL_KERNEL_LDG128 = 1, /* 128-bit streaming loads, grid-stride */
+  ACCEL_KERNEL_LDG256 = 2, /* 256-bit streaming loads (sm_100 LDG.256) */
+  ACCEL_KERNEL_TMA = 3     /* 1-D bulk-async (TMA) staged tiles + mbarrier ring */
+} accel_kernel;
+
+/* Hyper-parameters, by value. Scalars are fp32 exactly as TF's CPU kernels take
+ * them (TF-1.4 training_ops.cc ApplyGradientDescent / ApplyMomentum /
+ * ApplyAdamNonCuda; call sites mnist_replica.py:170, mnist_softmax.py:59). */
+typedef struct accel_hparams {
+  float lr;
+  float momentum;     /* Momentum */
+  float beta1;        /* Adam */
+  float beta2;        /* Adam */
+  float epsilon;      /* Adam */
+  float beta1_power;  /* Adam: beta1^t, initial value beta1 (TF adam.py _create_slots) */
+  float beta2_power;  /* Adam: beta2^t, initial value beta2 */
+  float clip_norm;    /* > 0 enables tf.clip_by_global_norm on the aggregated gradient */
+  int32_t use_nesterov; /* Momentum and Adam */
+  int32_t aggregate;    /* accel_aggregate */
+} accel_hparams;
+
+typedef struct accel_shard {
+  uint64_t offset; /* first element of the shard in the padded flat arena */
+  uint64_t count;  /* elements in the shard (padding included) */
+} accel_shard;
+
+/* ---- library ------------------------------------------------------------ */
+
+/* Library version (ACCEL_PS_VERSION). No reference counterpart: the reference
+ * reports its own version via version/version.go:3-6. */
+int accel_version(void);
+
+/* Message of the last failing call on this thread ("" if none). Mirrors Go's
+ * `error` return convention (pkg/controller/controller.go:237-240). */
+const char *accel_last_error(void);
+
+/* ---- context: PS task -> GPU map ---------------------------------------- */
+
+/* Create a context for n_ps parameter-server tasks. gpu_ordinals[i] is the CUDA
+ * device of PS task i; NULL means the identity map. n_ps is the `replicas` of
+ * the PS TFReplicaSpec (vendor/github.com/caicloud/kubeflow-clientset/apis/
+ * kubeflow/v1alpha1/types.go:58-79, read at pkg/tensorflow/distributed.go:140).
+ * No device is touched until a task is first used. */
+int accel_ctx_create(const int *gpu_ordinals, int n_ps, accel_ctx **out);
+int accel_ctx_destroy(accel_ctx *ctx);
+
+/* GPU ordinal serving PS task `task` (the "--task_index" emitted at
+ * pkg/tensorflow/distributed.go:151); negative accel_status on error. */
+int accel_ctx_gpu_of(const accel_ctx *ctx, int task);
+
+/* Select kernel variant and launch shape for subsequent applies. threads = CTA
+ * size (multiple of 32, <= 1024), ctas_per_sm = resident CTAs per SM of the
+ * persistent grid, unroll = independent vector loads per stream per thread.
+ * Any argument 0 keeps the built-in default. Benchmark/tuning knob; no
+ * reference counterpart. */
+int accel_ctx_set_kernel(accel_ctx *ctx, int kernel, int threads, int ctas_per_sm, int unroll);
+
+/* ---- variable -> PS task sharding (SURVEY §8 a7, §8 e) ------------------ */
+
+/* Flat mode: pad n_elems up to a multiple of n_ps*align_elems and split into
+ * n_ps equal contiguous shards (reduce-scatter ownership). out[n_ps]. */
+int accel_plan_flat(uint64_t n_elems, int n_ps, uint64_t align_elems, accel_shard *out,
+                    uint64_t *padded_elems);
+
+/* TF-faithful mode: tf.train.replica_device_setter's default round-robin —
+ * variable k (creation order) goes to PS task k mod n_ps
+ * (examples/workdir/mnist_replica.py:137-158). out_task[n_vars] receives the
+ * task, out_offset[n_vars] the variable's first element inside its task's
+ * bucket (each variable start rounded up to align_elems), bucket_elems[n_ps]
+ * the packed size of each bucket. `first_task` is the round-robin counter at
+ * the first of these variables (non-trainable variables created earlier, e.g.
+ * global_step at mnist_replica.py:142, advance it). */
+int accel_plan_round_robin(const uint64_t *var_elems, int n_vars, int n_ps, int first_task,
+                           uint64_t align_elems, int *out_task, uint64_t *out_offset,
+                           uint64_t *bucket_elems);
+
+/* ---- the hot path: fused N-way gradient aggregation + optimizer apply ---- */
+
+/* var -= lr * G, where G = aggregate(grads[0..n_workers-1]) (then clipped when
+ * hp->clip_norm > 0). One pass over HBM: n_workers*sizeof(g) + 8 bytes/element.
+ * Replaces TF-1.4 ConditionalAccumulator + ApplyGradientDescent on the PS CPU
+ * (reference call site examples/workdir/mnist_softmax.py:59; SURVEY §8 a8,a9).
+ * grads: host array of n_workers device pointers, each `count` elements of
+ * grad_dtype. grad_sumsq_dev: device pointer to sum(G^2) over the WHOLE model
+ * (all shards) for clipping; NULL with clip_norm > 0 makes the call compute it
+ * over [0,count) itself with accel_grad_sumsq into context scratch. */
+int accel_apply_sgd(accel_ctx *ctx, int task, float *var, const void *const *grads,
+                    int n_workers, int grad_dtype, uint64_t count, const accel_hparams *hp,
+                    const float *grad_sumsq_dev, accel_stream_t stream);
+
+/* accum = accum*momentum + G; var -= accum*lr
+ * (nesterov: var -= G*lr + accum*momentum*lr). n_workers*sizeof(g) + 16 B/elem.
+ * Replaces TF-1.4 ApplyMomentum. */
+int accel_apply_momentum(accel_ctx *ctx, int task, float *var, float *accum,
+                         const void *const *grads, int n_workers, int grad_dtype,
+                         uint64_t count, const accel_hparams *hp, const float *grad_sumsq_dev,
+                         accel_stream_t stream);
+
+/* alpha = lr*sqrt(1-beta2_power)/(1-beta1_power);
+ * m += (G-m)*(1-beta1); v += (G*G-v)*(1-beta2); var -= (m*alpha)/(sqrt(v)+epsilon)
+ * (nesterov: var -= ((G*(1-beta1) + beta1*m)*alpha)/(sqrt(v)+epsilon)).
+ * n_workers*sizeof(g) + 24 B/elem. Replaces TF-1.4 ApplyAdam
+ * (examples/workdir/mnist_replica.py:170). The caller advances
+ * the powers after the step with accel_adam_advance (TF does so in Python). */
+int accel_apply_adam(accel_ctx *ctx, int task, float *var, float *m, float *v,
+                     const void *const *grads, int n_workers, int grad_dtype, uint64_t count,
+                     const accel_hparams *hp, const float *grad_sumsq_dev,
+                     accel_stream_t stream);
+
+/* beta1_power *= beta1; beta2_power *= beta2 — TF-1.4 AdamOptimizer._finish,
+ * run once per step after all ApplyAdam ops (mnist_replica.py:170,184). */
+int accel_adam_advance(accel_hparams *hp);
+
+/* out_sumsq_dev[0] = sum over [0,count) of G^2, G = aggregate(grads), for
+ * tf.clip_by_global_norm. Deterministic for a given launch
+ * shape: per-thread fp32, warp-shuffle + shared-memory tree per CTA, CTA
+ * partials to context scratch, summed in index order in fp64 by the last CTA.
+ * Uses scratch global memory owned by the context (allocated at first use on
+ * the task's device). */
+int accel_grad_sumsq(accel_ctx *ctx, int task, const void *const *grads, int n_workers,
+                     int grad_dtype, uint64_t count, int aggregate, float *out_sumsq_dev,
+                     accel_stream_t stream);
+
+/* ---- one PS step with HOST buffers (the reference-facing call) ----------- */
+
+/* What a PS replica does per step when the workers' gradients arrive in host
+ * memory (the reference moves them by gRPC into PS host memory,
+ * examples/workdir/mnist_replica.py:251-264): copy the n_workers host gradient
+ * buffers to the GPU in chunks, run the fused aggregate+apply on each chunk as
+ * it lands, and copy the updated variables back to host_var_out (the workers'
+ * pull; may be NULL to skip). var/slot0/slot1 are DEVICE resident PS state
+ * (slot0 = accum or m, slot1 = v; NULL when unused). Copies and kernels are
+ * pipelined on context-owned streams; the call returns after the step is
+ * complete. Host buffers should be page-locked (accel_host_register). Global-
+ * norm clipping is not available on this entry point (it needs the whole
+ * gradient before the first chunk can be applied): clip_norm must be 0. */
+int accel_ps_step_host(accel_ctx *ctx, int task, int optimizer, float *var, float *slot0,
+                       float *slot1, const void *const *host_grads, int n_workers,
+                       int grad_dtype, uint64_t count, const accel_hparams *hp,
+                       float *host_var_out);
+
+/* Page-lock / unlock a host buffer so the step above copies at full PCIe rate. */
+int accel_host_register(void *host_ptr, size_t bytes);
+int accel_host_unregister(void *host_ptr);
+
+/* ---- placement: the contract pkg/tensorflow emits ------------------------ */
+
+typedef enum accel_replica_type { ACCEL_REPLICA_PS = 0, ACCEL_REPLICA_WORKER = 1 } accel_replica_type;
+
+/* Action types in the order of pkg/tensorflow/types.go:28-34. */
+typedef enum accel_action {
+  ACCEL_ACTION_ADD_PS = 0,
+  ACCEL_ACTION_ADD_PS_SERVICE = 1,
+  ACCEL_ACTION_ADD_WORKER = 2,
+  ACCEL_ACTION_ADD_WORKER_SERVICE = 3,
+  ACCEL_ACTION_DELETE = 4,
+  ACCEL_ACTION_NOTHING = 5
+} accel_action;
+
+typedef struct accel_event {
+  int32_t action; /* accel_action */
+  int32_t number;
+} accel_event;
+
+/* Desired-minus-actual replica counts -> ordered events, exactly as
+ * DistributedJob.Action (pkg/tensorflow/distributed.go:56-114). out must hold
+ * 4 events; *n_out receives the count; *composed is set to 1 when the
+ * reference would call compose() (new RuntimeID), else 0. */
+int accel_tfjob_action(int worker_replicas, int ps_replicas, int succeeded_workers,
+                       int worker_services, int ps_services, int active_workers, int active_ps,
+                       accel_event *out, int *n_out, int *composed);
+
+/* "<job>-<type lower-cased>-<index>" — DistributedJob.getServiceName
+ * (pkg/tensorflow/distributed.go:161-163). Returns the length written
+ * (excluding NUL) or a negative accel_status. */
+int accel_tfjob_service_key(const char *job_name, int replica_type, int index, char *buf,
+                            size_t buflen);
+
+/* The four argv strings of generateTFClusterSpec
+ * (pkg/tensorflow/distributed.go:127-159), NUL-separated in buf in the order
+ * --worker_hosts, --ps_hosts, --job_name, --task_index. worker_services[W] /
+ * ps_services[P] are the generated Service names (an entry may be "" — the
+ * reference then emits ":2222", distributed.go:131,142 with an empty map).
+ * Returns total bytes written including the four NULs, or negative status. */
+int accel_tfjob_cluster_spec(int worker_replicas, int ps_replicas,
+                             const char *const *worker_services, const char *const *ps_services,
+                             int replica_type, int index, char *buf, size_t buflen);
+
+/* Pod/Service label set of getLabels (+ "index" when index >= 0):
+ * distributed.go:121,165-167,221-228. Written as "key=value\n" lines sorted by
+ * key (Go maps are unordered). Returns bytes written excluding NUL. */
+int accel_tfjob_labels(const char *job_name, int replica_type, const char *runtime_id, int index,
+                       char *buf, size_t buflen);
+
+/* Parse the four flags a replica receives back into (job type, task index,
+ * host counts) — what examples/workdir/mnist_replica.py:107-115 does before
+ * tf.train.Server — and return the GPU ordinal for a PS task through ctx. */
+int accel_tfjob_parse_argv(const char *const *argv, int argc, int *replica_type, int *task_index,
+                           int *n_workers, int *n_ps);
+
+/* ---- multi-GPU: PS shards on the GPUs of one NVSwitch box (SURVEY §8 e) -- */
+
+#define ACCEL_IPC_HANDLE_BYTES 64
+typedef struct accel_ipc_handle {
+  unsigned char bytes[ACCEL_IPC_HANDLE_BYTES];
+} accel_ipc_handle;
+
+/* Export a device allocation for mapping by the other PS processes of the box,
+ * and map / unmap a peer's. (One process per GPU; handles travel over the
+ * rendezvous the launcher already has.) Replaces the reference's gRPC transport
+ * between pods (pkg/tensorflow/distributed.go:26-29,178-185, port 2222). */
+int accel_ipc_export(void *dev_ptr, accel_ipc_handle *out);
+int accel_ipc_open(const accel_ipc_handle *h, void **out_dev_ptr);
+int accel_ipc_close(void *dev_ptr);
+
+/* Peer views of one rank's multi-GPU step. All arrays have `world` entries
+ * indexed by PS task / rank; entry [rank] is this rank's own local buffer.
+ *   stage[r]  : fp32 [world][shard] receive slots on rank r — slot s holds the
+ *               partial gradient sum that rank s pushed for shard r;
+ *   var[r]    : fp32 [world*shard] full variable replica on rank r (the
+ *               workers' pull target);
+ *   flags[r]  : uint32 [ACCEL_SHARD_FLAG_WORDS] barrier words on rank r, zeroed
+ *               once by the owner before the first step. */
+#define ACCEL_SHARD_FLAG_WORDS 64
+typedef struct accel_peers {
+  int32_t rank;
+  int32_t world;
+  uint64_t shard_elems; /* elements per shard (padded arena / world) */
+  float *const *stage;
+  float *const *var;
+  uint32_t *const *flags;
+} accel_peers;
+
+/* Push (the worker->PS reduce-scatter, fused): sum this rank's n_workers local
+ * gradients over the whole arena and store the partial for shard r straight
+ * into rank r's stage slot [rank] over NVLink (own shard: local store), then
+ * signal every peer. One pass: reads n_workers*sizeof(g), writes 4 B/elem, of
+ * which (world-1)/world crosses NVLink. Replaces the gRPC RecvTensor of each
+ * gradient to its PS task. */
+int accel_shard_push(accel_ctx *ctx, const accel_peers *peers, const void *const *grads,
+                     int n_workers, int grad_dtype, accel_stream_t stream);
+
+/* Apply + pull (the PS apply and the PS->worker all-gather, fused): wait for all
+ * ranks' pushes, sum the `world` stage slots of this rank's shard in rank order,
+ * apply the optimizer to the shard's state (var shard lives inside var[rank]),
+ * and store the updated values into every rank's var replica over NVLink, then
+ * signal. slot0/slot1: this rank's shard-sized optimizer slots.
+ * n_contrib = total number of worker gradients summed over all ranks (the
+ * divisor for ACCEL_AGG_MEAN). Clipping: pass grad_sumsq_dev (global). */
+int accel_shard_apply_pull(accel_ctx *ctx, const accel_peers *peers, int optimizer, float *slot0,
+                           float *slot1, int n_contrib, const accel_hparams *hp,
+                           const float *grad_sumsq_dev, accel_stream_t stream);
+
+/* Block the stream until every rank's apply_pull of this step has landed in
+ * this rank's var replica (device-side wait on the peers' signals). */
+int accel_shard_wait_pull(accel_ctx *ctx, const accel_peers *peers, accel_stream_t stream);
+
+#ifdef __cplusplus
+} /* extern "C" */
+#endif
+#endif /* ACCEL_PS_H_ */

@@ -1,0 +1,4 @@
+// Instantiations of the fused aggregate+apply kernel: optimizer MOMENTUM, bf16 gradients.
+#include "ps_apply_inst.cuh"
+
+ACCEL_INSTANTIATE_APPLY_LDG(accel::OPT_MOMENTUM, accel::bf16_t)

@@ -1,0 +1,4 @@
+// Instantiations of the fused aggregate+apply kernel: optimizer SGD, f32 gradients.
+#include "ps_apply_inst.cuh"
+
+ACCEL_INSTANTIATE_APPLY_LDG(accel::OPT_SGD, float)

@@ -1,0 +1,134 @@
+// Sum of squares of the aggregated gradient, for tf.clip_by_global_norm
+// (TF-1.4 clip_ops.py global_norm — not in /root/reference).
+//
+// One read pass over the N worker gradients (N*sizeof(g) bytes/element). Each
+// thread accumulates G^2 in fp32 over a grid-strided set of vectors; the CTA
+// combines with warp shuffles and one shared-memory hop; CTA partials go to a
+// scratch array in global memory; the last CTA to finish (ticket counter) adds
+// the partials in index order in fp64 and writes one fp32 result. For a given
+// launch shape the result is bit-reproducible run to run.
+#include "ps_math.cuh"
+
+namespace accel {
+
+constexpr int kReduceThreads = 512;
+
+template <typename G, int NW>
+__global__ void __launch_bounds__(kReduceThreads)
+    ps_sumsq(const __grid_constant__ ApplyArgs a, float *__restrict__ partials,
+             unsigned int *__restrict__ ticket, float *__restrict__ out) {
+  constexpr int VE = Item<G, false>::VE;
+  const bool has_div = a.mean_div != 0.0f;
+  const uint64_t n_items = a.count / VE;
+  const int n = NW > 0 ? NW : a.n_workers;
+
+  float ss = 0.0f;
+  for (uint64_t it = static_cast<uint64_t>(blockIdx.x) * blockDim.x + threadIdx.x; it < n_items;
+       it += static_cast<uint64_t>(gridDim.x) * blockDim.x) {
+    float acc[VE];
+    if constexpr (NW > 0) {
+      float g[NW][VE];
+#pragma unroll
+      for (int w = 0; w < NW; ++w) load_grad_item<G, false>(a.grad[w], it, g[w]);
+#pragma unroll
+      for (int e = 0; e < VE; ++e) {
+        acc[e] = g[0][e];
+#pragma unroll
+        for (int w = 1; w < NW; ++w) acc[e] = __fadd_rn(acc[e], g[w][e]);
+      }
+    } else {
+      load_grad_item<G, false>(a.grad[0], it, acc);
+      for (int w = 1; w < n; ++w) {
+        float g[VE];
+        load_grad_item<G, false>(a.grad[w], it, g);
+#pragma unroll
+        for (int e = 0; e < VE; ++e) acc[e] = __fadd_rn(acc[e], g[e]);
+      }
+    }
+#pragma unroll
+    for (int e = 0; e < VE; ++e) {
+      float x = has_div ? __fdiv_rn(acc[e], a.mean_div) : acc[e];
+      ss = fmaf(x, x, ss);
+    }
+  }
+  // scalar tail
+  const uint64_t tail0 = n_items * VE;
+  if (blockIdx.x == 0 && tail0 + threadIdx.x < a.count) {
+    const uint64_t i = tail0 + threadIdx.x;
+    float sum = load_grad_scalar<G>(a.grad[0], i);
+    for (int w = 1; w < n; ++w) sum = __fadd_rn(sum, load_grad_scalar<G>(a.grad[w], i));
+    if (has_div) sum = __fdiv_rn(sum, a.mean_div);
+    ss = fmaf(sum, sum, ss);
+  }
+
+  // warp shuffle tree, then one shared-memory hop across the warps of the CTA
+#pragma unroll
+  for (int off = 16; off > 0; off >>= 1) ss += __shfl_xor_sync(0xffffffffu, ss, off);
+  __shared__ float warp_sum[kReduceThreads / 32];
+  __shared__ bool is_last;
+  const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
+  if (lane == 0) warp_sum[warp] = ss;
+  __syncthreads();
+  if (warp == 0) {
+    float t = lane < (blockDim.x >> 5) ? warp_sum[lane] : 0.0f;
+#pragma unroll
+    for (int off = 16; off > 0; off >>= 1) t += __shfl_xor_sync(0xffffffffu, t, off);
+    if (lane == 0) {
+      partials[blockIdx.x] = t;
+      __threadfence();
+      unsigned int done = atomicAdd(ticket, 1u);
+      is_last = (done == gridDim.x - 1);
+    }
+  }
+  __syncthreads();
+  if (is_last) {
+    // every partial is visible: the writers fenced before taking a ticket
+    __threadfence();
+    double t = 0.0;
+    for (unsigned int i = threadIdx.x; i < gridDim.x; i += blockDim.x)
+      t += static_cast<double>(__ldcg(partials + i));
+    // fixed-shape tree over the CTA in fp64
+    __shared__ double dsum[kReduceThreads / 32];
+#pragma unroll
+    for (int off = 16; off > 0; off >>= 1) t += __shfl_xor_sync(0xffffffffu, t, off);
+    if (lane == 0) dsum[warp] = t;
+    __syncthreads();
+    if (threadIdx.x == 0) {
+      double tot = 0.0;
+      for (int w = 0; w < (blockDim.x >> 5); ++w) tot += dsum[w];
+      out[0] = static_cast<float>(tot);
+      *ticket = 0u;  // ready for the next launch on this stream
+    }
+  }
+}
+
+template <typename G>
+static int launch_sumsq_g(const ApplyArgs &a, const TaskState &ts, float *out,
+                          cudaStream_t stream) {
+  constexpr int VE = Item<G, false>::VE;
+  const uint64_t items = a.count / VE;
+  uint64_t want = (items + kReduceThreads - 1) / kReduceThreads;
+  int grid = ts.sm_count * 4;  // 4 x 512 threads = all 2048 thread slots of an SM
+  if (grid > kReducePartials) grid = kReducePartials;
+  if (static_cast<uint64_t>(grid) > want) grid = want ? static_cast<int>(want) : 1;
+#define ACCEL_SUMSQ(NW) \
+  ps_sumsq<G, NW><<<grid, kReduceThreads, 0, stream>>>(a, ts.reduce_partials, ts.reduce_ticket, out)
+  switch (a.n_workers) {
+    case 1: ACCEL_SUMSQ(1); break;
+    case 2: ACCEL_SUMSQ(2); break;
+    case 4: ACCEL_SUMSQ(4); break;
+    case 8: ACCEL_SUMSQ(8); break;
+    default: ACCEL_SUMSQ(0); break;
+  }
+#undef ACCEL_SUMSQ
+  ACCEL_CUDA(cudaGetLastError());
+  return ACCEL_OK;
+}
+
+int launch_sumsq(const ApplyArgs &a, int grad_dtype, const TaskState &ts, float *out,
+                 cudaStream_t stream) {
+  return grad_dtype == ACCEL_BF16 ? launch_sumsq_g<bf16_t>(a, ts, out, stream)
+                                  : launch_sumsq_g<float>(a, ts, out, stream);
+}
+
+}  // namespace accel

@@ -1,0 +1,156 @@
+"""Placement contract (pkg/tensorflow/distributed.go) through the C ABI against the
+Python restatement and the hand-derived golden for examples/tfjob/dist.yml.
+Byte-exact strings and ints. No GPU."""
+import itertools
+
+import pytest
+
+from oracle import placement_oracle as PO
+
+
+@pytest.fixture(scope="module")
+def P(pkg):
+    return pkg.placement
+
+
+def test_dist_yml_first_sync_events(P, kat):
+    g = kat["placement_dist_yml"]
+    ev, composed = P.action(g["workers"], g["ps"])
+    assert [list(e) for e in ev] == g["events_first_sync"]
+    assert composed
+
+
+def test_dist_yml_cluster_spec_golden(P, kat):
+    g = kat["placement_dist_yml"]
+    sfx = {f"S{k}": s for k, s in enumerate(["bcdfg", "hjklm", "npqrs", "tvwxz", "24567", "89bcd"])}
+    wsvc = [PO.generate_name(P.service_key(g["job"], "Worker", i) + "-", sfx[f"S{i}"])
+            for i in range(4)]
+    psvc = [PO.generate_name(P.service_key(g["job"], "PS", i) + "-", sfx[f"S{4 + i}"])
+            for i in range(2)]
+    for i in range(2):
+        want = [t.format(i=i, **sfx) for t in g["ps_argv_template"]]
+        assert P.cluster_spec(4, 2, wsvc, psvc, "PS", i) == want
+        lab = {k: v.format(i=i, R="rt123") for k, v in g["ps_pod_labels"].items()}
+        assert P.labels(g["job"], "PS", "rt123", i) == lab
+    w = P.cluster_spec(4, 2, wsvc, psvc, "Worker", 3)
+    assert w[2:] == ["--job_name=worker", "--task_index=3"]
+    assert w[:2] == P.cluster_spec(4, 2, wsvc, psvc, "PS", 0)[:2]
+
+
+def test_config1_one_ps_two_workers(P):
+    """BASELINE config 1: 1 PS + 2 Workers."""
+    wsvc = ["mnist-worker-0-bbbbb", "mnist-worker-1-ccccc"]
+    psvc = ["mnist-ps-0-ddddd"]
+    assert P.cluster_spec(2, 1, wsvc, psvc, "PS", 0) == [
+        "--worker_hosts=mnist-worker-0-bbbbb:2222,mnist-worker-1-ccccc:2222",
+        "--ps_hosts=mnist-ps-0-ddddd:2222", "--job_name=ps", "--task_index=0"]
+    ev, _ = P.action(2, 1)
+    assert ev == [("ShouldAddWorkerService", 2), ("ShouldAddPSService", 1),
+                  ("ShouldAddWorker", 2), ("ShouldAddPS", 1)]
+
+
+@pytest.mark.parametrize("w,p,succ,wsvc,psvc,aw,ap", list(itertools.product(
+    [0, 2, 4], [0, 1, 2], [0, 1], [0, 2], [0, 1], [0, 1, 2, 4, 5], [0, 1, 3])))
+def test_action_matches_restatement(P, w, p, succ, wsvc, psvc, aw, ap):
+    assert P.action(w, p, succ, wsvc, psvc, aw, ap) == PO.action(w, p, succ, wsvc, psvc, aw, ap)
+
+
+def test_action_quirks(P):
+    # only the PS pods are missing: no compose, workers report Nothing (distributed.go:100-112)
+    ev, composed = P.action(4, 2, 0, 4, 2, 4, 1)
+    assert ev == [("Nothing", 0), ("ShouldAddPS", 1)] and not composed
+    # more active workers than expected: no worker event at all
+    assert P.action(2, 1, 0, 2, 1, 3, 1) == ([], False)
+    # succeeded workers shrink the pod count but not the host list (distributed.go:60,129)
+    ev, _ = P.action(4, 2, 3, 4, 2, 0, 2)
+    assert ev == [("ShouldAddWorker", 1)]
+    assert P.cluster_spec(4, 2, None, None, "Worker", 0)[0].count(":2222") == 4
+
+
+def test_cluster_spec_quirks(P):
+    # later sync: serviceNames is empty -> hosts degenerate to ":2222" (Appendix A.5)
+    assert P.cluster_spec(2, 1, None, None, "PS", 0) == [
+        "--worker_hosts=:2222,:2222", "--ps_hosts=:2222", "--job_name=ps", "--task_index=0"]
+    # zero replicas: the unconditional trim eats the '=' (distributed.go:137,148)
+    assert P.cluster_spec(0, 0, None, None, "Worker", 7) == [
+        "--worker_hosts", "--ps_hosts", "--job_name=worker", "--task_index=7"]
+    # job_name is lower-cased, the job_type label keeps the CRD's case (Appendix A.9)
+    assert P.labels("j", "Worker", "r")["job_type"] == "Worker"
+    assert "index" not in P.labels("j", "Worker", "r")
+    assert P.service_key("My-Job", "Worker", 12) == "My-Job-worker-12"
+
+
+@pytest.mark.parametrize("w,p", [(1, 1), (3, 2), (8, 8), (16, 3)])
+def test_cluster_spec_matches_restatement(P, w, p):
+    job = "job-x"
+    names = {}
+    for i in range(w):
+        names[PO.service_key(job, "Worker", i)] = f"{job}-worker-{i}-wwww{i % 10}"
+    for i in range(p):
+        names[PO.service_key(job, "PS", i)] = f"{job}-ps-{i}-pppp{i % 10}"
+    wsvc = [names[PO.service_key(job, "Worker", i)] for i in range(w)]
+    psvc = [names[PO.service_key(job, "PS", i)] for i in range(p)]
+    for typ, n in (("PS", p), ("Worker", w)):
+        for i in range(n):
+            assert P.cluster_spec(w, p, wsvc, psvc, typ, i) == \
+                PO.cluster_spec(job, w, p, names, typ, i)
+
+
+def test_parse_argv_round_trip(P):
+    argv = P.cluster_spec(4, 2, [f"w{i}" for i in range(4)], ["p0", "p1"], "PS", 1)
+    assert P.parse_argv(argv) == ("ps", 1, 4, 2)
+    argv = P.cluster_spec(4, 2, [f"w{i}" for i in range(4)], ["p0", "p1"], "Worker", 3)
+    assert P.parse_argv(argv) == ("worker", 3, 4, 2)
+
+
+def test_parse_argv_errors(P, pkg):
+    with pytest.raises(pkg.AccelError, match="job_name"):
+        P.parse_argv(["--task_index=0"])
+    with pytest.raises(pkg.AccelError, match="task_index"):
+        P.parse_argv(["--job_name=ps"])
+    with pytest.raises(pkg.AccelError):
+        P.parse_argv(["--job_name=chief", "--task_index=0"])
+
+
+def test_task_to_gpu_map(pkg):
+    ctx = pkg.Context(8)
+    assert [ctx.gpu_of(i) for i in range(8)] == list(range(8))      # identity by default
+    ctx = pkg.Context(2, [5, 3])
+    assert (ctx.gpu_of(0), ctx.gpu_of(1)) == (5, 3)
+    with pytest.raises(pkg.AccelError):
+        ctx.gpu_of(2)
+    with pytest.raises(pkg.AccelError):
+        pkg.Context(0)
+    with pytest.raises(pkg.AccelError):
+        pkg.Context(17)
+
+
+def test_round_robin_example_model(pkg):
+    """dist.yml P=2 with the example's variables (mnist_replica.py:142-158): global_step
+    takes task 0, so hid_w starts the trainable list at task 1."""
+    sizes = [784 * 100, 100, 100 * 10, 10]      # hid_w, hid_b, sm_w, sm_b
+    task, off, fill = pkg.plan_round_robin(sizes, 2, first_task=1)
+    assert task == [1, 0, 1, 0]
+    assert off == [0, 0, 78400, 100]
+    assert fill == [110, 79400]
+    # P = 1 (config 1): everything on task 0
+    task, off, fill = pkg.plan_round_robin(sizes, 1, first_task=1)
+    assert task == [0, 0, 0, 0] and fill == [79510]
+
+
+@pytest.mark.parametrize("n_ps", [1, 2, 3, 8])
+@pytest.mark.parametrize("align", [1, 8, 64])
+def test_round_robin_matches_restatement(pkg, n_ps, align):
+    sizes = [64, 9408, 64, 64, 4096, 36864, 2359296, 1000, 7, 1]
+    assert pkg.plan_round_robin(sizes, n_ps, 0, align) == \
+        tuple(PO.round_robin(sizes, n_ps, 0, align))
+
+
+@pytest.mark.parametrize("n,n_ps,align", [(25_557_032, 8, 8), (25_557_032, 2, 8),
+                                          (335_141_888, 8, 64), (10, 4, 1), (0, 2, 4)])
+def test_flat_plan(pkg, n, n_ps, align):
+    shards, padded = pkg.plan_flat(n, n_ps, align)
+    assert (shards, padded) == tuple(PO.flat(n, n_ps, align))
+    assert padded >= n and padded % (n_ps * align) == 0 and padded - n < n_ps * align
+    assert all(c == padded // n_ps for _, c in shards)
+    assert [o for o, _ in shards] == [r * (padded // n_ps) for r in range(n_ps)]
