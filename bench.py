@@ -100,9 +100,13 @@ def cpu_ps_rate(sample_elems: int, steps: int, warmup: int):
     cores = os.cpu_count() or 1
     orc = O.COracle(threads=cores)
     rng = np.random.default_rng(1234)
-    var = rng.standard_normal(sample_elems, dtype=np.float32)
-    grads = [rng.standard_normal(sample_elems, dtype=np.float32) * np.float32(0.01)
-             for _ in range(WORKERS)]
+    block = 1 << 20   # a random 4 MiB block tiled to size: init cost stays off the clock
+
+    def tiled(scale):
+        b = rng.standard_normal(block, dtype=np.float32) * np.float32(scale)
+        return np.resize(b, sample_elems)
+    var = tiled(1.0)
+    grads = [tiled(0.01) for _ in range(WORKERS)]
     acc = np.empty(sample_elems, dtype=np.float32)
     hp = O.HParams(lr=LR)
     for _ in range(warmup):
@@ -112,8 +116,11 @@ def cpu_ps_rate(sample_elems: int, steps: int, warmup: int):
         orc.ps_step(O.SGD, var, None, None, grads, hp, acc=acc)
     dt = (time.perf_counter() - t0) / steps
     gbs = WORKERS * sample_elems * 4 / dt / 1e9
-    sample = (f"{WORKERS} workers x {sample_elems} fp32 (1/{ELEMS // sample_elems} of the "
-              f"workload) x {steps} steps, C restatement of TF-1.4 ConditionalAccumulator + "
+    frac = "the whole workload" if sample_elems == ELEMS else \
+        f"1/{ELEMS // sample_elems} of the workload"
+    sample = (f"{WORKERS} workers x {sample_elems} fp32 ({frac}; working set "
+              f"{(WORKERS + 2) * sample_elems * 4 / 1e9:.1f} GB, beyond any host cache) x {steps} "
+              f"steps, C restatement of TF-1.4 ConditionalAccumulator + "
               f"ApplyGradientDescent, one pass per statement, {cores} threads")
     return gbs, dt, cores, sample
 
@@ -122,8 +129,8 @@ def run_reference(args):
     rank = int(os.environ.get("RANK", "0"))
     if rank != 0:
         return
-    sample = ELEMS // 8
-    gbs, dt, cores, desc = cpu_ps_rate(sample, max(args.steps, 1), max(args.warmup, 1))
+    sample = ELEMS     # full-size steps: ~0.1-0.3 s each on the box's host cores
+    gbs, dt, cores, desc = cpu_ps_rate(sample, max(args.steps, 1), min(max(args.warmup, 1), 3))
     line = {
         "impl": "reference", "metric": METRIC, "value": round(gbs, 3), "unit": UNIT,
         "n_gpus": args.gpus, "steps": args.steps, "warmup": args.warmup,
@@ -201,6 +208,19 @@ def run_single(args):
     achieved = alg_bytes / (avg_launch_ms * 1e-3) / 1e9
 
     # ---- e2e: the reference-facing call with HOST buffers -------------------------
+    e2e = cpu = None
+    if not args.no_e2e:
+        e2e = measure_e2e(args, pkg, ctx, var, grads, hp, grad_bytes)
+    if not args.no_cpu:
+        cpu_gbs, cpu_dt, cores, desc = cpu_ps_rate(ELEMS, 5, 1)
+        cpu = {"value": round(cpu_gbs, 3), "unit": UNIT, "cores": cores, "kind": "port",
+               "sample": desc}
+    emit_single(args, ms, value, alg_bytes, achieved, peak, peak_src, per_launch, avg_launch_ms,
+                cpu, e2e, clk)
+
+
+def measure_e2e(args, pkg, ctx, var, grads, hp, grad_bytes):
+    import torch
     e2e_steps = max(1, min(args.steps, args.e2e_steps))
     h_grads = [torch.empty(ELEMS, dtype=torch.float32).pin_memory() for _ in range(WORKERS)]
     for h, g in zip(h_grads, grads):
@@ -214,11 +234,15 @@ def run_single(args):
         ctx.ps_step_host(pkg.OPT_SGD, var, None, None, h_grads, hp, h_out)
     e2e_s = (time.perf_counter() - t0) / e2e_steps
     e2e_value = grad_bytes / e2e_s / 1e9
+    return {"value": round(e2e_value, 3), "unit": UNIT, "h2d_bytes_per_step": grad_bytes,
+            "d2h_bytes_per_step": ELEMS * 4, "ms_per_step": round(e2e_s * 1e3, 3),
+            "steps": e2e_steps,
+            "path": "accel_ps_step_host: pinned host gradients -> chunked H2D -> fused "
+                    "apply -> D2H of updated variables"}
 
-    # ---- cpu baseline: bounded sample on this box's host cores --------------------
-    del h_grads, h_out
-    cpu_gbs, cpu_dt, cores, desc = cpu_ps_rate(ELEMS // 8, 8, 2)
 
+def emit_single(args, ms, value, alg_bytes, achieved, peak, peak_src, per_launch, avg_launch_ms,
+                cpu, e2e, clk):
     line = {
         "metric": METRIC, "value": round(value, 2), "unit": UNIT, "n_gpus": 1,
         "steps": args.steps, "warmup": args.warmup, "ms_per_step": round(ms, 4),
@@ -232,13 +256,8 @@ def run_single(args):
                      "kernel": "ps_apply (fused 8-way sum + SGD)",
                      "launch_ms_min": round(min(per_launch), 4),
                      "launch_ms_avg": round(avg_launch_ms, 4)},
-        "cpu_baseline": {"value": round(cpu_gbs, 3), "unit": UNIT, "cores": cores,
-                         "kind": "port", "sample": desc},
-        "e2e": {"value": round(e2e_value, 3), "unit": UNIT, "h2d_bytes_per_step": grad_bytes,
-                "d2h_bytes_per_step": ELEMS * 4, "ms_per_step": round(e2e_s * 1e3, 3),
-                "steps": e2e_steps,
-                "path": "accel_ps_step_host: pinned host gradients -> chunked H2D -> fused "
-                        "apply -> D2H of updated variables"},
+        "cpu_baseline": cpu,
+        "e2e": e2e,
         "gpu_launches": args.steps,
         "clocks": clk,
     }
@@ -326,6 +345,8 @@ def main():
     ap.add_argument("--warmup", type=int, default=5)
     ap.add_argument("--impl", default="ours", choices=["ours", "reference"])
     ap.add_argument("--e2e-steps", type=int, default=5)
+    ap.add_argument("--no-e2e", action="store_true", help="skip the host-buffer leg (sweeps)")
+    ap.add_argument("--no-cpu", action="store_true", help="skip the CPU baseline leg (sweeps)")
     ap.add_argument("--mode", default="fused", choices=["fused", "nccl"])
     ap.add_argument("--kernel", default="", help="ldg128 | ldg256 | tma (default: auto)")
     ap.add_argument("--threads", type=int, default=0)

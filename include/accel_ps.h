@@ -287,6 +287,13 @@ int accel_ipc_export(void *dev_ptr, accel_ipc_handle *out);
 int accel_ipc_open(const accel_ipc_handle *h, void **out_dev_ptr);
 int accel_ipc_close(void *dev_ptr);
 
+/* Device memory that can be exported with accel_ipc_export: one whole allocation
+ * per buffer (a sub-range of a pooled allocator's block cannot be exported on
+ * its own), zero-filled. The caller owns it and frees it with accel_dev_free.
+ * No reference counterpart. */
+int accel_dev_alloc(size_t bytes, void **out_dev_ptr);
+int accel_dev_free(void *dev_ptr);
+
 /* Peer views of one rank's multi-GPU step. All arrays have `world` entries
  * indexed by PS task / rank; entry [rank] is this rank's own local buffer.
  *   stage[r]  : fp32 [world][shard] receive slots on rank r — slot s holds the
@@ -328,6 +335,11 @@ int accel_shard_apply_pull(accel_ctx *ctx, const accel_peers *peers, int optimiz
 /* Block the stream until every rank's apply_pull of this step has landed in
  * this rank's var replica (device-side wait on the peers' signals). */
 int accel_shard_wait_pull(accel_ctx *ctx, const accel_peers *peers, accel_stream_t stream);
+
+/* Synchronise the stream and report whether any cross-GPU wait of this rank
+ * timed out (every device-side wait is bounded; a rank that never arrives turns
+ * into ACCEL_ERR_STATE here instead of a hung GPU). */
+int accel_shard_check(accel_ctx *ctx, const accel_peers *peers, accel_stream_t stream);
 
 #ifdef __cplusplus
 } /* extern "C" */

@@ -31,7 +31,8 @@ SYMBOLS = [
     "accel_grad_sumsq", "accel_ps_step_host", "accel_host_register", "accel_host_unregister",
     "accel_tfjob_action", "accel_tfjob_service_key", "accel_tfjob_cluster_spec",
     "accel_tfjob_labels", "accel_tfjob_parse_argv", "accel_ipc_export", "accel_ipc_open",
-    "accel_ipc_close", "accel_shard_push", "accel_shard_apply_pull", "accel_shard_wait_pull",
+    "accel_ipc_close", "accel_dev_alloc", "accel_dev_free", "accel_shard_push",
+    "accel_shard_apply_pull", "accel_shard_wait_pull", "accel_shard_check",
 ]
 
 
@@ -129,6 +130,9 @@ def load_library() -> ctypes.CDLL:
     L.accel_shard_push.argtypes = [vp, ctypes.POINTER(Peers), pvp, i32, i32, vp]
     L.accel_shard_apply_pull.argtypes = [vp, ctypes.POINTER(Peers), i32, vp, vp, i32, php, vp, vp]
     L.accel_shard_wait_pull.argtypes = [vp, ctypes.POINTER(Peers), vp]
+    L.accel_shard_check.argtypes = [vp, ctypes.POINTER(Peers), vp]
+    L.accel_dev_alloc.argtypes = [ctypes.c_size_t, pvp]
+    L.accel_dev_free.argtypes = [vp]
     for name in SYMBOLS:
         fn = getattr(L, name)
         if name != "accel_last_error":

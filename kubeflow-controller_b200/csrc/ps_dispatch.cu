@@ -22,7 +22,16 @@ static int launch_opt(int optimizer, const ApplyArgs &a, bool wide, const Launch
 
 int launch_apply(int optimizer, int grad_dtype, const ApplyArgs &a, const TaskState &ts,
                  const Tuning &tune, cudaStream_t stream) {
-  int kernel = tune.kernel == ACCEL_KERNEL_AUTO ? ACCEL_KERNEL_LDG128 : tune.kernel;
+  int kernel = tune.kernel;
+  if (kernel == ACCEL_KERNEL_AUTO) {
+    // 256-bit loads measured ~5% faster than 128-bit on the BASELINE configs; they
+    // need 32-byte aligned buffers, which AUTO checks (an explicit LDG256 request
+    // with misaligned buffers is an error instead, see build_args).
+    uintptr_t bits = reinterpret_cast<uintptr_t>(a.var) | reinterpret_cast<uintptr_t>(a.slot0) |
+                     reinterpret_cast<uintptr_t>(a.slot1);
+    for (int w = 0; w < a.n_workers; ++w) bits |= reinterpret_cast<uintptr_t>(a.grad[w]);
+    kernel = (bits & 31) ? ACCEL_KERNEL_LDG128 : ACCEL_KERNEL_LDG256;
+  }
   if (kernel == ACCEL_KERNEL_TMA) {
     int rc = launch_apply_tma(optimizer, grad_dtype, a, ts, tune, stream);
     if (rc != ACCEL_ERR_STATE) return rc;  // ERR_STATE: shape not covered by the TMA variant

@@ -1,0 +1,115 @@
+"""The multi-GPU PS step (push -> apply_pull -> wait_pull) on ONE GPU: `world` ranks are
+emulated in turn inside one process (their "peer" buffers are local allocations), which
+exercises the whole data path and the flag protocol; real NVLink runs are bench.py --gpus N.
+Oracle: per-rank partial sums in worker order, partials added in rank order, then the
+TF-1.4 apply — bit-exact."""
+import numpy as np
+import pytest
+import torch
+
+from oracle import ps_oracle as O
+
+pytestmark = pytest.mark.gpu
+F = np.float32
+DEV = "cuda:0"
+
+
+def _dev(a):
+    if a.dtype == np.uint16:
+        return torch.from_numpy(a.view(np.int16)).to(DEV).view(torch.bfloat16)
+    return torch.from_numpy(a).to(DEV)
+
+
+def _oracle_hier(grads_per_rank, mean):
+    """aggregate per rank (worker order), then across ranks (rank order), divide by the total."""
+    partials = [O.numpy_aggregate(g, False) for g in grads_per_rank]
+    total = partials[0].copy()
+    for p in partials[1:]:
+        total = total + p
+    if mean:
+        total = total / F(sum(len(g) for g in grads_per_rank))
+    return total
+
+
+@pytest.mark.parametrize("world", [1, 2, 4, 8])
+@pytest.mark.parametrize("opt", [O.SGD, O.MOMENTUM, O.ADAM])
+@pytest.mark.parametrize("workers,bf16,mean", [(1, False, False), (8, False, True), (3, True, True)])
+def test_sharded_step_matches_oracle(pkg, world, opt, workers, bf16, mean):
+    from kubeflow_controller_b200 import sharded
+    elems = 100_003
+    agg = pkg.AGG_MEAN if mean else pkg.AGG_SUM
+    ranks = sharded.local_group(world, elems, opt,
+                                lambda: pkg.HParams(lr=0.01, momentum=0.9, aggregate=agg))
+    padded, shard = ranks[0].padded, ranks[0].shard
+    assert padded % (8 * world) == 0 and padded >= elems
+    rng = np.random.default_rng(world * 10 + workers)
+    var = rng.standard_normal(padded).astype(F)
+    s0 = np.zeros(padded, F)
+    s1 = np.zeros(padded, F)
+    for x in ranks:
+        x.var.copy_(_dev(var))
+    ohp = O.HParams(lr=0.01, momentum=0.9)
+    for step in range(3):
+        gpr = []
+        for r in range(world):
+            g = [(0.01 * rng.standard_normal(padded)).astype(F) for _ in range(workers)]
+            if bf16:
+                g = [O.f32_to_bf16_bits(x) for x in g]
+            gpr.append(g)
+        sharded.local_group_step(ranks, [[_dev(g) for g in gr] for gr in gpr])
+        O.numpy_apply(opt, var, s0, s1, _oracle_hier(gpr, mean), ohp)
+        ohp.advance()
+    torch.cuda.synchronize()
+    for x in ranks:
+        # every replica holds the whole updated arena (the pull is an all-gather)
+        assert np.array_equal(x.var.cpu().numpy(), var), f"rank {x.rank} replica differs"
+        lo = x.rank * shard
+        if opt >= O.MOMENTUM:
+            assert np.array_equal(x.slot0.cpu().numpy(), s0[lo:lo + shard])
+        if opt == O.ADAM:
+            assert np.array_equal(x.slot1.cpu().numpy(), s1[lo:lo + shard])
+        assert x.global_step == 3
+
+
+def test_sharded_clip_needs_global_sumsq(pkg):
+    from kubeflow_controller_b200 import sharded
+    ranks = sharded.local_group(2, 4096, pkg.OPT_SGD, lambda: pkg.HParams(lr=0.1, clip_norm=0.5))
+    g = [[torch.ones(ranks[0].padded, device=DEV)] for _ in ranks]
+    for x, gr in zip(ranks, g):
+        x.push(gr)
+    with pytest.raises(pkg.AccelError, match="grad_sumsq_dev"):
+        ranks[0].apply_pull(2)
+    # with the global sum of squares the clip is the TF formula on the summed gradient
+    ss = torch.tensor([float(ranks[0].padded) * 4.0], device=DEV)   # (1+1)^2 per element
+    for x in ranks:
+        x.apply_pull(2, sumsq=ss)
+    for x in ranks:
+        x.wait_pull()
+        x.check()
+    scale = O.numpy_clip_scale(F(ss.item()), 0.5)
+    want = F(0.0) - (F(2.0) * scale) * F(0.1)
+    assert torch.all(ranks[1].var == float(want))
+
+
+def test_wait_times_out_instead_of_hanging(pkg):
+    """A rank whose peer never pushes must come back with an error, not hang the GPU."""
+    from kubeflow_controller_b200 import sharded
+    ranks = sharded.local_group(2, 4096, pkg.OPT_SGD, lambda: pkg.HParams(lr=0.1))
+    ranks[0].push([torch.ones(ranks[0].padded, device=DEV)])
+    ranks[0].apply_pull(2)            # rank 1 never pushed: bounded wait (2 s), then bail out
+    with pytest.raises(pkg.AccelError, match="timed out"):
+        ranks[0].check()
+    assert not ranks[0].var.any(), "a timed-out step must not touch the variables"
+
+
+def test_shard_argument_errors(pkg):
+    from kubeflow_controller_b200 import sharded
+    ranks = sharded.local_group(2, 4096, pkg.OPT_ADAM, lambda: pkg.HParams())
+    x = ranks[0]
+    with pytest.raises(pkg.AccelError, match="before any"):
+        x.wait_pull()
+    with pytest.raises(pkg.AccelError, match="aligned"):
+        x.push([torch.ones(x.padded + 1, device=DEV)[1:]])
+    bad = pkg.accel.Peers(0, 2, 12, x._stage_arr, x._var_arr, x._flags_arr)
+    with pytest.raises(pkg.AccelError, match="multiple of 8"):
+        x.push([torch.ones(x.padded, device=DEV)], peers=bad)
