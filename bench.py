@@ -291,6 +291,8 @@ def run_sharded(args):
     stream = torch.cuda.current_stream()
     for _ in range(args.warmup):
         sps.step(grads, stream)
+    if sps.mode == "fused":
+        sps.check(stream)      # a rank that never arrived surfaces here, not as a hang
     torch.cuda.synchronize()
     clocks = ClockSampler(local)
     if rank == 0:

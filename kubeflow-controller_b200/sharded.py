@@ -89,6 +89,8 @@ class ShardedPS:
         self.elems = elems
         self.padded, self.shard = shard_layout(elems, world)
         self.ctx = ctx or accel.Context(world, gpu_ordinals)
+        # the nccl-mode pre-sum is a world-of-one push on THIS rank's GPU
+        self.solo_ctx = accel.Context(1, [device_index])
         self.lib = accel.load_library()
         self.global_step = 0
         # exportable buffers: full variable replica, receive slots, flag words
@@ -138,8 +140,9 @@ class ShardedPS:
 
     # ---- the three phases (exposed so a single GPU can emulate several ranks in turn) ----
     def push(self, grads, stream=None, peers=None):
+        ctx = self.solo_ctx if peers is self.solo else self.ctx
         accel.check(self.lib.accel_shard_push(
-            self.ctx.handle, ctypes.byref(peers or self.peers), accel._grad_array(grads),
+            ctx.handle, ctypes.byref(peers or self.peers), accel._grad_array(grads),
             len(grads), accel._grad_dtype(grads[0]), accel._stream_handle(stream)))
 
     def apply_pull(self, n_contrib: int, sumsq=None, stream=None):
