@@ -195,6 +195,36 @@ int accel_grad_sumsq(accel_ctx *ctx, int task, const void *const *grads, int n_w
                      int grad_dtype, uint64_t count, int aggregate, float *out_sumsq_dev,
                      accel_stream_t stream);
 
+/* accel_grad_sumsq for callers that must not allocate device memory. It has no
+ * counterpart in the reference. Who needs it: a PS process living inside a
+ * framework that has already handed all of HBM to its own arena at start-up (a
+ * later cudaMalloc by this library, such as the scratch accel_ctx allocates on
+ * a task's first use, would simply fail there), and callers on a step loop
+ * that cannot afford the device-wide synchronisation a cudaMalloc/cudaFree
+ * implies. This entry point takes no context, runs on the CURRENT device, and
+ * calls no cudaMalloc, cudaFree or other allocating routine: its scratch (one
+ * fp32 partial per CTA and a ticket word, 16.25 KiB) is a static device array
+ * inside the library, present on every GPU that loads the library until the
+ * process exits.
+ *   - Limit: count <= ACCEL_SUMSQ_STATIC_MAX_ELEMS (2^28 elements per worker
+ *     gradient, i.e. 4096 CTAs of 65536 elements); larger counts are refused
+ *     with ACCEL_ERR_INVALID — split the range and add the results, or use
+ *     accel_grad_sumsq.
+ *   - The first call on each device looks up the array's device address
+ *     (cudaGetSymbolAddress, once per device); make that first call during
+ *     set-up, before any stream capture begins.
+ *   - All calls on a device share the one array. The ticket word is cleared on
+ *     the stream at the start of every call; calls whose kernels could overlap
+ *     on the GPU (different streams, or different host threads without
+ *     ordering) race on it — serialise them.
+ *   - Result: same definition as accel_grad_sumsq, same tolerance (the CTA
+ *     count differs, so the last bits of the fp32 sum may differ); for a given
+ *     count it is reproducible and does not depend on the GPU's SM count. */
+#define ACCEL_SUMSQ_STATIC_MAX_ELEMS 268435456ull
+int accel_grad_sumsq_static(const void *const *grads, int n_workers, int grad_dtype,
+                            uint64_t count, int aggregate, float *out_sumsq_dev,
+                            accel_stream_t stream);
+
 /* ---- one PS step with HOST buffers (the reference-facing call) ----------- */
 
 /* What a PS replica does per step when the workers' gradients arrive in host

@@ -28,7 +28,7 @@ SYMBOLS = [
     "accel_version", "accel_last_error", "accel_ctx_create", "accel_ctx_destroy",
     "accel_ctx_gpu_of", "accel_ctx_set_kernel", "accel_plan_flat", "accel_plan_round_robin",
     "accel_apply_sgd", "accel_apply_momentum", "accel_apply_adam", "accel_adam_advance",
-    "accel_grad_sumsq", "accel_ps_step_host", "accel_host_register", "accel_host_unregister",
+    "accel_grad_sumsq", "accel_grad_sumsq_static", "accel_ps_step_host", "accel_host_register", "accel_host_unregister",
     "accel_tfjob_action", "accel_tfjob_service_key", "accel_tfjob_cluster_spec",
     "accel_tfjob_labels", "accel_tfjob_parse_argv", "accel_ipc_export", "accel_ipc_open",
     "accel_ipc_close", "accel_dev_alloc", "accel_dev_free", "accel_shard_push",
@@ -110,6 +110,7 @@ def load_library() -> ctypes.CDLL:
     L.accel_apply_adam.argtypes = [vp, i32, vp, vp, vp, pvp, i32, i32, u64, php, vp, vp]
     L.accel_adam_advance.argtypes = [php]
     L.accel_grad_sumsq.argtypes = [vp, i32, pvp, i32, i32, u64, i32, vp, vp]
+    L.accel_grad_sumsq_static.argtypes = [pvp, i32, i32, u64, i32, vp, vp]
     L.accel_ps_step_host.argtypes = [vp, i32, i32, vp, vp, vp, pvp, i32, i32, u64, php, vp]
     L.accel_host_register.argtypes = [vp, ctypes.c_size_t]
     L.accel_host_unregister.argtypes = [vp]
@@ -261,6 +262,19 @@ class Context:
                                           _ptr(slot1), _grad_array(host_grads), len(host_grads),
                                           _grad_dtype(host_grads[0]), n, ctypes.byref(hp),
                                           _ptr(host_var_out)))
+
+
+SUMSQ_STATIC_MAX_ELEMS = 1 << 28
+
+
+def grad_sumsq_static(grads, out, aggregate=AGG_SUM, count=None, stream=None) -> None:
+    """accel_grad_sumsq_static: the sum of squares of the aggregated gradient for callers
+    that must not allocate device memory (no context; scratch is a static array inside
+    the library; runs on the current device; count <= SUMSQ_STATIC_MAX_ELEMS)."""
+    n = grads[0].numel() if count is None else count
+    check(load_library().accel_grad_sumsq_static(_grad_array(grads), len(grads),
+                                                 _grad_dtype(grads[0]), n, aggregate, _ptr(out),
+                                                 _stream_handle(stream)))
 
 
 def adam_advance(hp: HParams) -> None:

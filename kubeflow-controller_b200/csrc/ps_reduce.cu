@@ -7,6 +7,8 @@
 // scratch array in global memory; the last CTA to finish (ticket counter) adds
 // the partials in index order in fp64 and writes one fp32 result. For a given
 // launch shape the result is bit-reproducible run to run.
+#include <mutex>
+
 #include "ps_math.cuh"
 
 namespace accel {
@@ -132,3 +134,109 @@ int launch_sumsq(const ApplyArgs &a, int grad_dtype, const TaskState &ts, float 
 }
 
 }  // namespace accel
+
+// ---- the entry point that allocates nothing -----------------------------------------
+//
+// Same kernel, but its scratch (CTA partials + the ticket word) is this file-scope
+// device array instead of memory the context allocated. Every GPU that loads the
+// library carries these 16.25 KiB until the process exits.
+namespace accel {
+
+constexpr int kStaticMaxCtas = 4096;                    // one fp32 partial per CTA
+constexpr uint64_t kStaticElemsPerCta = 65536;          // elements a CTA strides over
+constexpr size_t kStaticTicketOffset = kStaticMaxCtas * sizeof(float);
+static_assert(uint64_t{kStaticMaxCtas} * kStaticElemsPerCta == ACCEL_SUMSQ_STATIC_MAX_ELEMS,
+              "header constant out of step with the scratch size");
+
+static __device__ __align__(256) unsigned char g_sumsq_static_scratch[kStaticTicketOffset + 256];
+
+// In host code `g_sumsq_static_scratch` is only a handle for the runtime, not an address a
+// kernel can use; the device address is looked up once per device and kept here.
+constexpr int kMaxDevices = 64;
+static std::mutex g_static_mu;
+static unsigned char *g_static_addr[kMaxDevices] = {};
+
+static int static_scratch_for_current_device(unsigned char **out) {
+  int dev = -1;
+  ACCEL_CUDA(cudaGetDevice(&dev));
+  if (dev < 0 || dev >= kMaxDevices)
+    return fail(ACCEL_ERR_INVALID, "device ordinal %d out of range [0,%d)", dev, kMaxDevices);
+  std::lock_guard<std::mutex> lock(g_static_mu);
+  if (!g_static_addr[dev]) {
+    void *p = nullptr;
+    ACCEL_CUDA(cudaGetSymbolAddress(&p, g_sumsq_static_scratch));
+    g_static_addr[dev] = static_cast<unsigned char *>(p);
+  }
+  *out = g_static_addr[dev];
+  return ACCEL_OK;
+}
+
+template <typename G>
+static int launch_sumsq_static(const ApplyArgs &a, int grid, float *partials, unsigned int *ticket,
+                               float *out, cudaStream_t stream) {
+#define ACCEL_SUMSQ_STATIC(NW) \
+  ps_sumsq<G, NW><<<grid, kReduceThreads, 0, stream>>>(a, partials, ticket, out)
+  switch (a.n_workers) {
+    case 1: ACCEL_SUMSQ_STATIC(1); break;
+    case 2: ACCEL_SUMSQ_STATIC(2); break;
+    case 4: ACCEL_SUMSQ_STATIC(4); break;
+    case 8: ACCEL_SUMSQ_STATIC(8); break;
+    default: ACCEL_SUMSQ_STATIC(0); break;
+  }
+#undef ACCEL_SUMSQ_STATIC
+  ACCEL_CUDA(cudaGetLastError());
+  return ACCEL_OK;
+}
+
+}  // namespace accel
+
+extern "C" int accel_grad_sumsq_static(const void *const *grads, int n_workers, int grad_dtype,
+                                       uint64_t count, int aggregate, float *out_sumsq_dev,
+                                       accel_stream_t stream) {
+  using namespace accel;
+  if (!grads) return fail(ACCEL_ERR_INVALID, "grads is NULL");
+  if (!out_sumsq_dev) return fail(ACCEL_ERR_INVALID, "out_sumsq_dev is NULL");
+  if (n_workers < 1 || n_workers > ACCEL_MAX_WORKERS)
+    return fail(ACCEL_ERR_INVALID, "n_workers %d out of range [1,%d]", n_workers,
+                ACCEL_MAX_WORKERS);
+  if (grad_dtype != ACCEL_F32 && grad_dtype != ACCEL_BF16)
+    return fail(ACCEL_ERR_INVALID, "unknown grad_dtype %d", grad_dtype);
+  if (aggregate != ACCEL_AGG_SUM && aggregate != ACCEL_AGG_MEAN)
+    return fail(ACCEL_ERR_INVALID, "unknown aggregate %d", aggregate);
+  if (count > ACCEL_SUMSQ_STATIC_MAX_ELEMS)
+    return fail(ACCEL_ERR_INVALID,
+                "count %llu is beyond the %llu elements the built-in scratch of "
+                "accel_grad_sumsq_static covers; split the range (sums of squares add) or use "
+                "accel_grad_sumsq",
+                static_cast<unsigned long long>(count),
+                static_cast<unsigned long long>(ACCEL_SUMSQ_STATIC_MAX_ELEMS));
+  ApplyArgs a;
+  memset(&a, 0, sizeof(a));
+  for (int w = 0; w < n_workers; ++w) {
+    if (!grads[w]) return fail(ACCEL_ERR_INVALID, "grads[%d] is NULL", w);
+    if (reinterpret_cast<uintptr_t>(grads[w]) & 15)
+      return fail(ACCEL_ERR_ALIGN, "grads[%d] must be 16-byte aligned", w);
+    a.grad[w] = grads[w];
+  }
+  a.count = count;
+  a.n_workers = n_workers;
+  a.mean_div = aggregate == ACCEL_AGG_MEAN ? static_cast<float>(n_workers) : 0.0f;
+  cudaStream_t s = static_cast<cudaStream_t>(stream);
+  if (count == 0) {
+    ACCEL_CUDA(cudaMemsetAsync(out_sumsq_dev, 0, sizeof(float), s));
+    return ACCEL_OK;
+  }
+  unsigned char *scratch = nullptr;
+  int rc = static_scratch_for_current_device(&scratch);
+  if (rc) return rc;
+  float *partials = reinterpret_cast<float *>(scratch);
+  unsigned int *ticket = reinterpret_cast<unsigned int *>(scratch + kStaticTicketOffset);
+  // The array still holds whatever the previous call left. Partials need no clearing (each
+  // CTA of this launch overwrites its own before the last CTA reads them); the ticket must
+  // start at zero, also after a launch that was cut short.
+  ACCEL_CUDA(cudaMemsetAsync(ticket, 0, sizeof(unsigned int), s));
+  const int grid = static_cast<int>((count + kStaticElemsPerCta - 1) / kStaticElemsPerCta);
+  return grad_dtype == ACCEL_BF16
+             ? launch_sumsq_static<bf16_t>(a, grid, partials, ticket, out_sumsq_dev, s)
+             : launch_sumsq_static<float>(a, grid, partials, ticket, out_sumsq_dev, s);
+}
