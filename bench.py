@@ -280,7 +280,9 @@ def run_sharded(args):
     dev = torch.device("cuda", local)
     torch.cuda.set_device(dev)
     dist.init_process_group("nccl", device_id=dev)
-    sps = ShardedPS(rank, world, local, ELEMS, pkg.OPT_SGD, pkg.HParams(lr=LR), mode=args.mode)
+    sps = ShardedPS(rank, world, local, ELEMS, pkg.OPT_SGD, pkg.HParams(lr=LR), mode=args.mode,
+                    n_chunks=args.chunks or None, rendezvous=args.rendezvous,
+                    multicast=args.multicast)
     gen = torch.Generator(device=dev)
     gen.manual_seed(42)
     sps.var.copy_(torch.randn(sps.padded, device=dev, generator=gen))
@@ -291,7 +293,7 @@ def run_sharded(args):
     stream = torch.cuda.current_stream()
     for _ in range(args.warmup):
         sps.step(grads, stream)
-    if sps.mode == "fused":
+    if sps.mode != "nccl":
         sps.check(stream)      # a rank that never arrived surfaces here, not as a hang
     torch.cuda.synchronize()
     clocks = ClockSampler(local)
@@ -323,7 +325,8 @@ def run_sharded(args):
             "n_gpus": world, "steps": args.steps, "warmup": args.warmup,
             "ms_per_step": round(ms, 4), "higher_is_better": True, "scaling": "weak",
             "vs_baseline": None, "dtype": "f32", "data": "synthetic",
-            "config": dict(workload_config(world), mode=sps.mode),
+            "config": dict(workload_config(world), mode=sps.mode, chunks=sps.n_chunks,
+                           rendezvous=args.rendezvous, multicast=bool(sps.multicast_ptr)),
             "steps_per_s": round(1e3 / ms, 2),
             "roofline": {"bound": "hbm", "achieved": round(hbm_bytes / (ms * 1e-3) / 1e9, 2),
                          "peak": peak, "unit": "GB/s",
@@ -349,7 +352,12 @@ def main():
     ap.add_argument("--e2e-steps", type=int, default=5)
     ap.add_argument("--no-e2e", action="store_true", help="skip the host-buffer leg (sweeps)")
     ap.add_argument("--no-cpu", action="store_true", help="skip the CPU baseline leg (sweeps)")
-    ap.add_argument("--mode", default="fused", choices=["fused", "nccl"])
+    ap.add_argument("--mode", default="fused", choices=["fused", "streams", "nccl"])
+    ap.add_argument("--chunks", type=int, default=0,
+                    help="pipeline slices of the sharded step (0 = the harness default per world)")
+    ap.add_argument("--rendezvous", default="ipc", choices=["ipc", "symm"])
+    ap.add_argument("--multicast", action="store_true",
+                    help="pull through an NVSwitch multicast mapping (symm rendezvous only)")
     ap.add_argument("--kernel", default="", help="ldg128 | ldg256 | tma (default: auto)")
     ap.add_argument("--threads", type=int, default=0)
     ap.add_argument("--ctas", type=int, default=0)

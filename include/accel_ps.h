@@ -331,40 +331,85 @@ int accel_dev_free(void *dev_ptr);
  *   var[r]    : fp32 [world*shard] full variable replica on rank r (the
  *               workers' pull target);
  *   flags[r]  : uint32 [ACCEL_SHARD_FLAG_WORDS] barrier words on rank r, zeroed
- *               once by the owner before the first step. */
-#define ACCEL_SHARD_FLAG_WORDS 64
+ *               once by the owner before the first step;
+ *   var_multicast : optional NVSwitch multicast mapping covering every rank's
+ *               var replica (one store reaches all replicas, in-switch); NULL
+ *               makes the pull `world` unicast peer stores. */
+#define ACCEL_SHARD_FLAG_WORDS 256
 typedef struct accel_peers {
   int32_t rank;
   int32_t world;
-  uint64_t shard_elems; /* elements per shard (padded arena / world) */
+  uint64_t shard_elems; /* elements per shard (padded arena / world), multiple of 8 */
   float *const *stage;
   float *const *var;
   uint32_t *const *flags;
+  float *var_multicast;
 } accel_peers;
 
 /* Push (the worker->PS reduce-scatter, fused): sum this rank's n_workers local
- * gradients over the whole arena and store the partial for shard r straight
- * into rank r's stage slot [rank] over NVLink (own shard: local store), then
- * signal every peer. One pass: reads n_workers*sizeof(g), writes 4 B/elem, of
- * which (world-1)/world crosses NVLink. Replaces the gRPC RecvTensor of each
- * gradient to its PS task. */
+ * gradients and store the partial for shard c straight into rank c's stage
+ * slot [rank] over NVLink (own shard: local store), then signal every peer.
+ * One pass: reads n_workers*sizeof(g), writes 4 B/elem, of which
+ * (world-1)/world crosses NVLink. Replaces the gRPC RecvTensor of each gradient
+ * to its PS task. [sub_begin, sub_begin+sub_count) selects the
+ * same slice of EVERY shard (multiples of 8; sub_count 0 = whole shards), so a
+ * step can be cut into slices and pipelined. Every push opens a new epoch,
+ * returned in *epoch_out (may be NULL). */
 int accel_shard_push(accel_ctx *ctx, const accel_peers *peers, const void *const *grads,
-                     int n_workers, int grad_dtype, accel_stream_t stream);
+                     int n_workers, int grad_dtype, uint64_t sub_begin, uint64_t sub_count,
+                     accel_stream_t stream, uint32_t *epoch_out);
 
 /* Apply + pull (the PS apply and the PS->worker all-gather, fused): wait for all
- * ranks' pushes, sum the `world` stage slots of this rank's shard in rank order,
- * apply the optimizer to the shard's state (var shard lives inside var[rank]),
- * and store the updated values into every rank's var replica over NVLink, then
- * signal. slot0/slot1: this rank's shard-sized optimizer slots.
- * n_contrib = total number of worker gradients summed over all ranks (the
- * divisor for ACCEL_AGG_MEAN). Clipping: pass grad_sumsq_dev (global). */
+ * ranks' pushes of `epoch` (0 = the latest push of this rank), sum the `world`
+ * stage slots of this rank's shard slice in rank order, apply the optimizer to
+ * the slice's state (the var shard lives inside var[rank]), and store the
+ * updated values into every rank's var replica over NVLink, then signal.
+ * slot0/slot1: this rank's shard-sized optimizer slots. n_contrib = total number
+ * of worker gradients summed over all ranks (the divisor for ACCEL_AGG_MEAN).
+ * Clipping needs grad_sumsq_dev (the global sum of squares). */
 int accel_shard_apply_pull(accel_ctx *ctx, const accel_peers *peers, int optimizer, float *slot0,
                            float *slot1, int n_contrib, const accel_hparams *hp,
-                           const float *grad_sumsq_dev, accel_stream_t stream);
+                           const float *grad_sumsq_dev, uint64_t sub_begin, uint64_t sub_count,
+                           uint32_t epoch, accel_stream_t stream);
 
-/* Block the stream until every rank's apply_pull of this step has landed in
- * this rank's var replica (device-side wait on the peers' signals). */
-int accel_shard_wait_pull(accel_ctx *ctx, const accel_peers *peers, accel_stream_t stream);
+/* Block the stream until every rank's apply_pull of `epoch` (0 = latest) has
+ * landed in this rank's var replica (device-side, bounded wait). */
+int accel_shard_wait_pull(accel_ctx *ctx, const accel_peers *peers, uint32_t epoch,
+                          accel_stream_t stream);
+
+/* The whole step as one call, pipelined: the arena is cut into n_chunks slices;
+ * push of slice k+1 (HBM-bound) runs on `stream` while apply_pull of slice k
+ * (NVLink-bound) runs on a context-owned second stream; ends with wait_pull on
+ * `stream`. This is the per-step call of a PS replica in a sharded job
+ * (what examples/workdir/mnist_replica.py:256 triggers on the PS side). */
+int accel_shard_step(accel_ctx *ctx, const accel_peers *peers, int optimizer, float *slot0,
+                     float *slot1, const void *const *grads, int n_workers, int grad_dtype,
+                     int n_contrib, const accel_hparams *hp, const float *grad_sumsq_dev,
+                     int n_chunks, accel_stream_t stream);
+
+/* The whole step as ONE cooperative kernel per GPU: push, apply, pull and the
+ * closing wait overlapped slice by slice inside the kernel (every CTA pushes
+ * slice k, then applies whichever earlier slices have arrived from all ranks,
+ * and only blocks once its own pushes are issued). Same results as
+ * accel_shard_step, bit for bit. n_slices in [1,64]. Needs all CTAs resident:
+ * the launch is cooperative and fails rather than deadlocks if the GPU cannot
+ * hold the grid. */
+int accel_shard_step_fused(accel_ctx *ctx, const accel_peers *peers, int optimizer, float *slot0,
+                           float *slot1, const void *const *grads, int n_workers, int grad_dtype,
+                           int n_contrib, const accel_hparams *hp, const float *grad_sumsq_dev,
+                           int n_slices, accel_stream_t stream);
+
+/* Development / CI vehicle for the one-kernel step: all n_ranks (<= 8) ranks of a
+ * group whose buffers live on ONE GPU are played by one cooperative launch (CTA
+ * group g is rank g), so the cross-rank waits are between co-resident CTAs.
+ * peers_of_rank[r] is rank r's view; slot0/slot1/grads are per-rank arrays. No
+ * reference counterpart. */
+int accel_shard_step_local_group(accel_ctx *ctx, const accel_peers *const *peers_of_rank,
+                                 int n_ranks, int optimizer, float *const *slot0,
+                                 float *const *slot1, const void *const *const *grads,
+                                 int n_workers, int grad_dtype, int n_contrib,
+                                 const accel_hparams *hp, const float *grad_sumsq_dev,
+                                 int n_slices, accel_stream_t stream);
 
 /* Synchronise the stream and report whether any cross-GPU wait of this rank
  * timed out (every device-side wait is bounded; a rank that never arrives turns

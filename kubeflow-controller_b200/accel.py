@@ -32,7 +32,8 @@ SYMBOLS = [
     "accel_tfjob_action", "accel_tfjob_service_key", "accel_tfjob_cluster_spec",
     "accel_tfjob_labels", "accel_tfjob_parse_argv", "accel_ipc_export", "accel_ipc_open",
     "accel_ipc_close", "accel_dev_alloc", "accel_dev_free", "accel_shard_push",
-    "accel_shard_apply_pull", "accel_shard_wait_pull", "accel_shard_check",
+    "accel_shard_apply_pull", "accel_shard_wait_pull", "accel_shard_step", "accel_shard_step_fused",
+    "accel_shard_step_local_group", "accel_shard_check",
 ]
 
 
@@ -76,7 +77,8 @@ class Peers(ctypes.Structure):
                 ("shard_elems", ctypes.c_uint64),
                 ("stage", ctypes.POINTER(ctypes.c_void_p)),
                 ("var", ctypes.POINTER(ctypes.c_void_p)),
-                ("flags", ctypes.POINTER(ctypes.c_void_p))]
+                ("flags", ctypes.POINTER(ctypes.c_void_p)),
+                ("var_multicast", ctypes.c_void_p)]
 
 
 _lib = None
@@ -128,9 +130,18 @@ def load_library() -> ctypes.CDLL:
     L.accel_ipc_export.argtypes = [vp, ctypes.POINTER(IpcHandle)]
     L.accel_ipc_open.argtypes = [ctypes.POINTER(IpcHandle), pvp]
     L.accel_ipc_close.argtypes = [vp]
-    L.accel_shard_push.argtypes = [vp, ctypes.POINTER(Peers), pvp, i32, i32, vp]
-    L.accel_shard_apply_pull.argtypes = [vp, ctypes.POINTER(Peers), i32, vp, vp, i32, php, vp, vp]
-    L.accel_shard_wait_pull.argtypes = [vp, ctypes.POINTER(Peers), vp]
+    u32 = ctypes.c_uint32
+    L.accel_shard_push.argtypes = [vp, ctypes.POINTER(Peers), pvp, i32, i32, u64, u64, vp,
+                                   ctypes.POINTER(u32)]
+    L.accel_shard_apply_pull.argtypes = [vp, ctypes.POINTER(Peers), i32, vp, vp, i32, php, vp,
+                                         u64, u64, u32, vp]
+    L.accel_shard_wait_pull.argtypes = [vp, ctypes.POINTER(Peers), u32, vp]
+    L.accel_shard_step.argtypes = [vp, ctypes.POINTER(Peers), i32, vp, vp, pvp, i32, i32, i32, php,
+                                   vp, i32, vp]
+    L.accel_shard_step_fused.argtypes = L.accel_shard_step.argtypes
+    L.accel_shard_step_local_group.argtypes = [vp, ctypes.POINTER(ctypes.POINTER(Peers)), i32, i32,
+                                               pvp, pvp, ctypes.POINTER(pvp), i32, i32, i32, php,
+                                               vp, i32, vp]
     L.accel_shard_check.argtypes = [vp, ctypes.POINTER(Peers), vp]
     L.accel_dev_alloc.argtypes = [ctypes.c_size_t, pvp]
     L.accel_dev_free.argtypes = [vp]

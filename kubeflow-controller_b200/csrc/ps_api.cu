@@ -73,6 +73,9 @@ static void task_release(TaskState &ts) {
   if (ts.copy_in) cudaStreamDestroy(ts.copy_in);
   if (ts.compute) cudaStreamDestroy(ts.compute);
   if (ts.copy_out) cudaStreamDestroy(ts.copy_out);
+  if (ts.shard_aux) cudaStreamDestroy(ts.shard_aux);
+  if (ts.shard_ev_push) cudaEventDestroy(ts.shard_ev_push);
+  if (ts.shard_ev_done) cudaEventDestroy(ts.shard_ev_done);
   ts = TaskState();
 }
 

@@ -48,6 +48,8 @@ struct TaskState {
   float *out_buf[2] = {nullptr, nullptr};
   size_t out_bytes = 0;
   unsigned int shard_epoch = 0;  // barrier generation of the multi-GPU step
+  cudaStream_t shard_aux = nullptr;  // apply_pull of slice k runs here beside push of slice k+1
+  cudaEvent_t shard_ev_push = nullptr, shard_ev_done = nullptr;
 };
 
 }  // namespace accel

@@ -15,100 +15,9 @@
 // peers with release stores at system scope after a last-CTA ticket, and polled
 // with acquire loads. Every poll is bounded (kSpinTimeoutNs): on timeout the
 // kernel records an error in the status word and returns without touching data.
-#include "ps_math.cuh"
+#include "ps_shard.cuh"
 
 namespace accel {
-
-constexpr int kFlagPush = 0;     // [0,16): push of rank s has landed (epoch)
-constexpr int kFlagPull = 16;    // [16,32): apply_pull of rank s has landed
-constexpr int kFlagTicketPush = 32;
-constexpr int kFlagTicketApply = 33;
-constexpr int kFlagStatus = 48;  // 0 ok, else error code | (waited-for rank << 8)
-constexpr unsigned long long kSpinTimeoutNs = 2000000000ull;  // 2 s
-
-struct ShardArgs {
-  float *stage[ACCEL_MAX_PS];
-  float *var[ACCEL_MAX_PS];
-  uint32_t *flags[ACCEL_MAX_PS];
-  const void *grad[ACCEL_MAX_WORKERS];
-  float *slot0;
-  float *slot1;
-  const float *sumsq;
-  uint64_t shard;  // elements per shard, multiple of 8
-  int rank, world, n_workers;
-  uint32_t epoch;
-  // optimizer scalars (see ApplyArgs)
-  int use_nesterov;
-  float lr, momentum, beta1, one_minus_beta1, one_minus_beta2, alpha, epsilon, mean_div, clip_norm;
-};
-
-__device__ __forceinline__ uint32_t ld_acquire_sys(const uint32_t *p) {
-  uint32_t v;
-  asm volatile("ld.acquire.sys.global.u32 %0, [%1];" : "=r"(v) : "l"(p) : "memory");
-  return v;
-}
-__device__ __forceinline__ void st_release_sys(uint32_t *p, uint32_t v) {
-  asm volatile("st.release.sys.global.u32 [%0], %1;" ::"l"(p), "r"(v) : "memory");
-}
-__device__ __forceinline__ unsigned long long globaltimer_ns() {
-  unsigned long long t;
-  asm volatile("mov.u64 %0, %globaltimer;" : "=l"(t));
-  return t;
-}
-
-// Thread 0 of the CTA waits until flags[base + s] has reached `epoch` for every
-// rank s. Returns false (for the whole CTA) on timeout or if another CTA
-// already recorded a failure.
-__device__ bool wait_all(uint32_t *flags, int base, int world, uint32_t epoch) {
-  __shared__ int ok;
-  if (threadIdx.x == 0) {
-    ok = 1;
-    const unsigned long long t0 = globaltimer_ns();
-    for (int s = 0; s < world && ok; ++s) {
-      // epochs only grow; signed distance handles the 32-bit wrap
-      while (static_cast<int32_t>(ld_acquire_sys(flags + base + s) - epoch) < 0) {
-        if (globaltimer_ns() - t0 > kSpinTimeoutNs || ld_acquire_sys(flags + kFlagStatus) != 0) {
-          atomicCAS(flags + kFlagStatus, 0u, 1u | (static_cast<uint32_t>(s) << 8) |
-                                                 (static_cast<uint32_t>(base) << 16));
-          ok = 0;
-          break;
-        }
-        __nanosleep(200);
-      }
-    }
-  }
-  __syncthreads();
-  return ok != 0;
-}
-
-// After the CTA's stores: the last CTA of the grid publishes `epoch` into word
-// [word_base + rank] of every rank's flags.
-__device__ void signal_all(const ShardArgs &a, int ticket_word, int word_base) {
-  __syncthreads();
-  if (threadIdx.x == 0) {
-    __threadfence_system();  // this CTA's peer stores are ordered before the ticket
-    uint32_t *local = a.flags[a.rank];
-    const unsigned int done = atomicAdd(local + ticket_word, 1u);
-    if (done == gridDim.x - 1) {
-      local[ticket_word] = 0;  // ready for the next launch
-      __threadfence_system();  // all CTAs' tickets (and their stores) happen-before the flags
-      for (int p = 0; p < a.world; ++p) st_release_sys(a.flags[p] + word_base + a.rank, a.epoch);
-    }
-  }
-}
-
-__device__ __forceinline__ void st_256(float *p, const float (&o)[8]) {
-  asm volatile("st.global.v8.f32 [%0], {%1,%2,%3,%4,%5,%6,%7,%8};" ::"l"(p), "f"(o[0]), "f"(o[1]),
-               "f"(o[2]), "f"(o[3]), "f"(o[4]), "f"(o[5]), "f"(o[6]), "f"(o[7])
-               : "memory");
-}
-__device__ __forceinline__ void ld_256_plain(const float *p, float (&o)[8]) {
-  asm volatile("ld.global.L1::no_allocate.v8.f32 {%0,%1,%2,%3,%4,%5,%6,%7}, [%8];"
-               : "=f"(o[0]), "=f"(o[1]), "=f"(o[2]), "=f"(o[3]), "=f"(o[4]), "=f"(o[5]),
-                 "=f"(o[6]), "=f"(o[7])
-               : "l"(p)
-               : "memory");
-}
 
 // ---- push: local N-way sum fused with the reduce-scatter -----------------------
 // Items of 8 elements. Logical item j maps to arena element
@@ -118,22 +27,30 @@ __device__ __forceinline__ void ld_256_plain(const float *p, float (&o)[8]) {
 template <typename G, int NW, int U>
 __global__ void __launch_bounds__(512) ps_push(const __grid_constant__ ShardArgs a) {
   const uint64_t shard_items = a.shard / 8;
-  const uint64_t n_items = shard_items * a.world;
-  const uint64_t rot = shard_items * ((a.rank + 1) % a.world);
+  const uint64_t sub_items = a.sub_count / 8;   // items per shard in this launch
+  const uint64_t sub_first = a.sub_begin / 8;
+  const uint64_t n_items = sub_items * a.world;
   const uint64_t tile = static_cast<uint64_t>(blockDim.x) * U;
   const int n = NW > 0 ? NW : a.n_workers;
 
   for (uint64_t base = static_cast<uint64_t>(blockIdx.x) * tile; base < n_items;
        base += static_cast<uint64_t>(gridDim.x) * tile) {
-    uint64_t item[U];
+    uint64_t item[U];   // arena item (8 elements) this thread sums
+    uint64_t dst[U];    // item index inside the owner's stage slot [rank]
+    int owner[U];
     bool ok[U];
     float acc[U][8];
 #pragma unroll
     for (int j = 0; j < U; ++j) {
       const uint64_t l = base + static_cast<uint64_t>(j) * blockDim.x + threadIdx.x;
       ok[j] = l < n_items;
-      uint64_t p = l + rot;
-      item[j] = p >= n_items ? p - n_items : p;
+      const uint64_t k = l / sub_items;          // k-th destination of this rank's rotation
+      int c = a.rank + 1 + static_cast<int>(k);
+      if (c >= a.world) c -= a.world;
+      owner[j] = ok[j] ? c : a.rank;
+      const uint64_t within = sub_first + (l - k * sub_items);
+      item[j] = static_cast<uint64_t>(owner[j]) * shard_items + within;
+      dst[j] = static_cast<uint64_t>(a.rank) * shard_items + within;
     }
     if constexpr (NW > 0) {
       float g[NW][U][8];
@@ -166,13 +83,8 @@ __global__ void __launch_bounds__(512) ps_push(const __grid_constant__ ShardArgs
       }
     }
 #pragma unroll
-    for (int j = 0; j < U; ++j) {
-      if (!ok[j]) continue;
-      const uint64_t c = item[j] / shard_items;           // destination rank = shard owner
-      const uint64_t in_shard = item[j] - c * shard_items;
-      float *dst = a.stage[c] + (static_cast<uint64_t>(a.rank) * shard_items + in_shard) * 8;
-      st_256(dst, acc[j]);
-    }
+    for (int j = 0; j < U; ++j)
+      if (ok[j]) st_256(a.stage[owner[j]] + dst[j] * 8, acc[j]);
   }
   signal_all(a, kFlagTicketPush, kFlagPush);
 }
@@ -199,16 +111,17 @@ __global__ void __launch_bounds__(512) ps_apply_pull(const __grid_constant__ Sha
   const Scalars sc = make_scalars(sa);
 
   const uint64_t shard_items = a.shard / 8;
+  const uint64_t sub_first = a.sub_begin / 8, sub_end = sub_first + a.sub_count / 8;
   const float *stage = a.stage[a.rank];
   const uint64_t var_off = static_cast<uint64_t>(a.rank) * a.shard;
   const uint64_t tile = static_cast<uint64_t>(blockDim.x) * U;
 
-  for (uint64_t base = static_cast<uint64_t>(blockIdx.x) * tile; base < shard_items;
+  for (uint64_t base = sub_first + static_cast<uint64_t>(blockIdx.x) * tile; base < sub_end;
        base += static_cast<uint64_t>(gridDim.x) * tile) {
 #pragma unroll
     for (int j = 0; j < U; ++j) {
       const uint64_t it = base + static_cast<uint64_t>(j) * blockDim.x + threadIdx.x;
-      if (it >= shard_items) continue;
+      if (it >= sub_end) continue;
       float acc[8], v[8], s0[8], s1[8];
       ld_state_256(a.var[a.rank] + var_off + it * 8, v);
       if constexpr (SLOTS >= 1) ld_state_256(a.slot0 + it * 8, s0);
@@ -231,11 +144,17 @@ __global__ void __launch_bounds__(512) ps_apply_pull(const __grid_constant__ Sha
       for (int e = 0; e < 8; ++e) update<OPT>(v[e], s0[e], s1[e], finish_grad(acc[e], sc), sc);
       if constexpr (SLOTS >= 1) st_state_256(a.slot0 + it * 8, s0);
       if constexpr (SLOTS >= 2) st_state_256(a.slot1 + it * 8, s1);
-      // the pull: own replica first, then the peers starting with the right-hand neighbour
-      for (int k = 0; k < a.world; ++k) {
-        int p = a.rank + k;
-        if (p >= a.world) p -= a.world;
-        st_256(a.var[p] + var_off + it * 8, v);
+      if (a.var_mc != nullptr) {
+        // the pull through the switch: one multicast store lands in every rank's replica
+        st_multimem_128(a.var_mc + var_off + it * 8, v);
+        st_multimem_128(a.var_mc + var_off + it * 8 + 4, v + 4);
+      } else {
+        // the pull as unicast peer stores: own replica first, then the right-hand neighbours
+        for (int k = 0; k < a.world; ++k) {
+          int p = a.rank + k;
+          if (p >= a.world) p -= a.world;
+          st_256(a.var[p] + var_off + it * 8, v);
+        }
       }
     }
   }
@@ -262,7 +181,7 @@ static int launch_push(const ShardArgs &a, int grid, cudaStream_t s) {
   return ACCEL_OK;
 }
 
-static int fill_peers(const accel_peers *peers, ShardArgs *a) {
+int fill_peers(const accel_peers *peers, uint64_t sub_begin, uint64_t sub_count, ShardArgs *a) {
   if (!peers) return fail(ACCEL_ERR_INVALID, "peers is NULL");
   if (peers->world < 1 || peers->world > ACCEL_MAX_PS)
     return fail(ACCEL_ERR_INVALID, "world %d out of range [1,%d]", peers->world, ACCEL_MAX_PS);
@@ -273,6 +192,16 @@ static int fill_peers(const accel_peers *peers, ShardArgs *a) {
                 static_cast<unsigned long long>(peers->shard_elems));
   if (!peers->stage || !peers->var || !peers->flags)
     return fail(ACCEL_ERR_INVALID, "peers->stage/var/flags is NULL");
+  if (sub_count == 0) {  // the whole shard
+    sub_begin = 0;
+    sub_count = peers->shard_elems;
+  }
+  if (sub_begin % 8 || sub_count % 8 || sub_begin + sub_count > peers->shard_elems)
+    return fail(ACCEL_ERR_INVALID,
+                "sub-range [%llu, +%llu) must be multiples of 8 inside the shard of %llu elements",
+                static_cast<unsigned long long>(sub_begin),
+                static_cast<unsigned long long>(sub_count),
+                static_cast<unsigned long long>(peers->shard_elems));
   memset(a, 0, sizeof(*a));
   for (int r = 0; r < peers->world; ++r) {
     if (!peers->stage[r] || !peers->var[r] || !peers->flags[r])
@@ -283,9 +212,134 @@ static int fill_peers(const accel_peers *peers, ShardArgs *a) {
     a->var[r] = peers->var[r];
     a->flags[r] = peers->flags[r];
   }
+  if (reinterpret_cast<uintptr_t>(peers->var_multicast) & 31)
+    return fail(ACCEL_ERR_ALIGN, "var_multicast must be 32-byte aligned");
+  a->var_mc = peers->var_multicast;
   a->rank = peers->rank;
   a->world = peers->world;
   a->shard = peers->shard_elems;
+  a->sub_begin = sub_begin;
+  a->sub_count = sub_count;
+  return ACCEL_OK;
+}
+
+int fill_grads(const void *const *grads, int n_workers, int grad_dtype, ShardArgs *a) {
+  if (!grads) return fail(ACCEL_ERR_INVALID, "grads is NULL");
+  if (n_workers < 1 || n_workers > ACCEL_MAX_WORKERS)
+    return fail(ACCEL_ERR_INVALID, "n_workers %d out of range [1,%d]", n_workers,
+                ACCEL_MAX_WORKERS);
+  if (grad_dtype != ACCEL_F32 && grad_dtype != ACCEL_BF16)
+    return fail(ACCEL_ERR_INVALID, "unknown grad_dtype %d", grad_dtype);
+  for (int w = 0; w < n_workers; ++w) {
+    if (!grads[w]) return fail(ACCEL_ERR_INVALID, "grads[%d] is NULL", w);
+    if (reinterpret_cast<uintptr_t>(grads[w]) & 31)
+      return fail(ACCEL_ERR_ALIGN, "grads[%d] must be 32-byte aligned", w);
+    a->grad[w] = grads[w];
+  }
+  a->n_workers = n_workers;
+  return ACCEL_OK;
+}
+
+int fill_optimizer(int optimizer, float *slot0, float *slot1, int n_contrib,
+                   const accel_hparams *hp, const float *grad_sumsq_dev, ShardArgs *a) {
+  if (!hp) return fail(ACCEL_ERR_INVALID, "hparams is NULL");
+  if (optimizer < ACCEL_OPT_SGD || optimizer > ACCEL_OPT_ADAM)
+    return fail(ACCEL_ERR_INVALID, "unknown optimizer %d", optimizer);
+  if (optimizer >= ACCEL_OPT_MOMENTUM && !slot0)
+    return fail(ACCEL_ERR_INVALID, "optimizer slot 0 (accum / m) is NULL");
+  if (optimizer == ACCEL_OPT_ADAM && !slot1)
+    return fail(ACCEL_ERR_INVALID, "optimizer slot 1 (v) is NULL");
+  if ((reinterpret_cast<uintptr_t>(slot0) | reinterpret_cast<uintptr_t>(slot1)) & 31)
+    return fail(ACCEL_ERR_ALIGN, "slots must be 32-byte aligned");
+  if (hp->clip_norm > 0.0f && !grad_sumsq_dev)
+    return fail(ACCEL_ERR_INVALID,
+                "clip_norm > 0 needs grad_sumsq_dev: the global norm spans all shards");
+  if (hp->aggregate != ACCEL_AGG_SUM && hp->aggregate != ACCEL_AGG_MEAN)
+    return fail(ACCEL_ERR_INVALID, "unknown aggregate %d", hp->aggregate);
+  if (n_contrib < 1) return fail(ACCEL_ERR_INVALID, "n_contrib must be >= 1");
+  a->slot0 = slot0;
+  a->slot1 = slot1;
+  a->sumsq = grad_sumsq_dev;
+  a->use_nesterov = hp->use_nesterov ? 1 : 0;
+  a->lr = hp->lr;
+  a->momentum = hp->momentum;
+  a->beta1 = hp->beta1;
+  a->one_minus_beta1 = 1.0f - hp->beta1;
+  a->one_minus_beta2 = 1.0f - hp->beta2;
+  a->epsilon = hp->epsilon;
+  a->alpha = 0.0f;
+  if (optimizer == ACCEL_OPT_ADAM) {
+    const float num = hp->lr * sqrtf(1.0f - hp->beta2_power);
+    a->alpha = num / (1.0f - hp->beta1_power);
+  }
+  a->mean_div = hp->aggregate == ACCEL_AGG_MEAN ? static_cast<float>(n_contrib) : 0.0f;
+  a->clip_norm = hp->clip_norm > 0.0f ? hp->clip_norm : 0.0f;
+  return ACCEL_OK;
+}
+
+static int grid_for(const TaskState &ts, uint64_t items, int ctas_per_sm) {
+  int grid = ts.sm_count * ctas_per_sm;
+  const uint64_t want = (items + 255) / 256;
+  if (static_cast<uint64_t>(grid) > want) grid = static_cast<int>(want);
+  return grid < 1 ? 1 : grid;
+}
+
+// ctas_per_sm: 2 fills the register file (2 x 256 threads x 96 registers); the pipelined step
+// passes 1 so that the apply_pull CTAs of the previous slice can be resident beside the push.
+static int do_push(accel_ctx *ctx, const accel_peers *peers, const void *const *grads,
+                   int n_workers, int grad_dtype, uint64_t sub_begin, uint64_t sub_count,
+                   cudaStream_t s, uint32_t *epoch_out, int ctas_per_sm = 2) {
+  ShardArgs a;
+  int rc = fill_peers(peers, sub_begin, sub_count, &a);
+  if (rc) return rc;
+  TaskState *ts = nullptr;
+  rc = task_state(ctx, peers->rank, &ts);
+  if (rc) return rc;
+  rc = fill_grads(grads, n_workers, grad_dtype, &a);
+  if (rc) return rc;
+  a.epoch = ++ts->shard_epoch;  // every push opens a new epoch
+  if (epoch_out) *epoch_out = a.epoch;
+  const int grid = grid_for(*ts, a.sub_count / 8 * a.world, ctas_per_sm);
+  return grad_dtype == ACCEL_BF16 ? launch_push<bf16_t>(a, grid, s) : launch_push<float>(a, grid, s);
+}
+
+static int do_apply_pull(accel_ctx *ctx, const accel_peers *peers, int optimizer, float *slot0,
+                         float *slot1, int n_contrib, const accel_hparams *hp,
+                         const float *grad_sumsq_dev, uint64_t sub_begin, uint64_t sub_count,
+                         uint32_t epoch, cudaStream_t s, int ctas_per_sm = 4) {
+  ShardArgs a;
+  int rc = fill_peers(peers, sub_begin, sub_count, &a);
+  if (rc) return rc;
+  TaskState *ts = nullptr;
+  rc = task_state(ctx, peers->rank, &ts);
+  if (rc) return rc;
+  rc = fill_optimizer(optimizer, slot0, slot1, n_contrib, hp, grad_sumsq_dev, &a);
+  if (rc) return rc;
+  if (ts->shard_epoch == 0)
+    return fail(ACCEL_ERR_STATE, "accel_shard_apply_pull before any accel_shard_push");
+  a.epoch = epoch ? epoch : ts->shard_epoch;
+  const int grid = grid_for(*ts, a.sub_count / 8, ctas_per_sm);
+  switch (optimizer) {
+    case ACCEL_OPT_SGD: ps_apply_pull<OPT_SGD, 1><<<grid, 256, 0, s>>>(a); break;
+    case ACCEL_OPT_MOMENTUM: ps_apply_pull<OPT_MOMENTUM, 1><<<grid, 256, 0, s>>>(a); break;
+    default: ps_apply_pull<OPT_ADAM, 1><<<grid, 256, 0, s>>>(a); break;
+  }
+  ACCEL_CUDA(cudaGetLastError());
+  return ACCEL_OK;
+}
+
+static int do_wait_pull(accel_ctx *ctx, const accel_peers *peers, uint32_t epoch, cudaStream_t s) {
+  ShardArgs a;
+  int rc = fill_peers(peers, 0, 0, &a);
+  if (rc) return rc;
+  TaskState *ts = nullptr;
+  rc = task_state(ctx, peers->rank, &ts);
+  if (rc) return rc;
+  if (ts->shard_epoch == 0)
+    return fail(ACCEL_ERR_STATE, "accel_shard_wait_pull before any accel_shard_push");
+  a.epoch = epoch ? epoch : ts->shard_epoch;
+  ps_wait_pull<<<1, 32, 0, s>>>(a);
+  ACCEL_CUDA(cudaGetLastError());
   return ACCEL_OK;
 }
 
@@ -308,113 +362,73 @@ int accel_dev_free(void *ptr) {
 }
 
 int accel_shard_push(accel_ctx *ctx, const accel_peers *peers, const void *const *grads,
-                     int n_workers, int grad_dtype, accel_stream_t stream) {
-  ShardArgs a;
-  int rc = fill_peers(peers, &a);
-  if (rc) return rc;
-  TaskState *ts = nullptr;
-  rc = task_state(ctx, peers->rank, &ts);
-  if (rc) return rc;
-  if (!grads) return fail(ACCEL_ERR_INVALID, "grads is NULL");
-  if (n_workers < 1 || n_workers > ACCEL_MAX_WORKERS)
-    return fail(ACCEL_ERR_INVALID, "n_workers %d out of range [1,%d]", n_workers,
-                ACCEL_MAX_WORKERS);
-  if (grad_dtype != ACCEL_F32 && grad_dtype != ACCEL_BF16)
-    return fail(ACCEL_ERR_INVALID, "unknown grad_dtype %d", grad_dtype);
-  for (int w = 0; w < n_workers; ++w) {
-    if (!grads[w]) return fail(ACCEL_ERR_INVALID, "grads[%d] is NULL", w);
-    if (reinterpret_cast<uintptr_t>(grads[w]) & 31)
-      return fail(ACCEL_ERR_ALIGN, "grads[%d] must be 32-byte aligned", w);
-    a.grad[w] = grads[w];
-  }
-  a.n_workers = n_workers;
-  a.epoch = ++ts->shard_epoch;  // one epoch per step: push, apply_pull and wait_pull share it
-  const uint64_t items = a.shard / 8 * a.world;
-  int grid = ts->sm_count * 2;
-  const uint64_t want = (items + 255) / 256;
-  if (static_cast<uint64_t>(grid) > want) grid = static_cast<int>(want);
-  cudaStream_t s = static_cast<cudaStream_t>(stream);
-  return grad_dtype == ACCEL_BF16 ? launch_push<bf16_t>(a, grid, s) : launch_push<float>(a, grid, s);
+                     int n_workers, int grad_dtype, uint64_t sub_begin, uint64_t sub_count,
+                     accel_stream_t stream, uint32_t *epoch_out) {
+  return do_push(ctx, peers, grads, n_workers, grad_dtype, sub_begin, sub_count,
+                 static_cast<cudaStream_t>(stream), epoch_out);
 }
 
 int accel_shard_apply_pull(accel_ctx *ctx, const accel_peers *peers, int optimizer, float *slot0,
                            float *slot1, int n_contrib, const accel_hparams *hp,
-                           const float *grad_sumsq_dev, accel_stream_t stream) {
-  ShardArgs a;
-  int rc = fill_peers(peers, &a);
-  if (rc) return rc;
-  TaskState *ts = nullptr;
-  rc = task_state(ctx, peers->rank, &ts);
-  if (rc) return rc;
-  if (!hp) return fail(ACCEL_ERR_INVALID, "hparams is NULL");
-  if (optimizer < ACCEL_OPT_SGD || optimizer > ACCEL_OPT_ADAM)
-    return fail(ACCEL_ERR_INVALID, "unknown optimizer %d", optimizer);
-  if (optimizer >= ACCEL_OPT_MOMENTUM && !slot0)
-    return fail(ACCEL_ERR_INVALID, "optimizer slot 0 (accum / m) is NULL");
-  if (optimizer == ACCEL_OPT_ADAM && !slot1)
-    return fail(ACCEL_ERR_INVALID, "optimizer slot 1 (v) is NULL");
-  if ((reinterpret_cast<uintptr_t>(slot0) | reinterpret_cast<uintptr_t>(slot1)) & 31)
-    return fail(ACCEL_ERR_ALIGN, "slots must be 32-byte aligned");
-  if (hp->clip_norm > 0.0f && !grad_sumsq_dev)
-    return fail(ACCEL_ERR_INVALID,
-                "clip_norm > 0 needs grad_sumsq_dev: the global norm spans all shards");
-  if (n_contrib < 1) return fail(ACCEL_ERR_INVALID, "n_contrib must be >= 1");
-  if (ts->shard_epoch == 0)
-    return fail(ACCEL_ERR_STATE, "accel_shard_apply_pull before any accel_shard_push");
-  a.slot0 = slot0;
-  a.slot1 = slot1;
-  a.sumsq = grad_sumsq_dev;
-  a.epoch = ts->shard_epoch;
-  a.use_nesterov = hp->use_nesterov ? 1 : 0;
-  a.lr = hp->lr;
-  a.momentum = hp->momentum;
-  a.beta1 = hp->beta1;
-  a.one_minus_beta1 = 1.0f - hp->beta1;
-  a.one_minus_beta2 = 1.0f - hp->beta2;
-  a.epsilon = hp->epsilon;
-  if (optimizer == ACCEL_OPT_ADAM) {
-    const float num = hp->lr * sqrtf(1.0f - hp->beta2_power);
-    a.alpha = num / (1.0f - hp->beta1_power);
-  }
-  a.mean_div = hp->aggregate == ACCEL_AGG_MEAN ? static_cast<float>(n_contrib) : 0.0f;
-  a.clip_norm = hp->clip_norm > 0.0f ? hp->clip_norm : 0.0f;
-  const uint64_t items = a.shard / 8;
-  int grid = ts->sm_count * 4;
-  const uint64_t want = (items + 255) / 256;
-  if (static_cast<uint64_t>(grid) > want) grid = static_cast<int>(want);
-  cudaStream_t s = static_cast<cudaStream_t>(stream);
-  switch (optimizer) {
-    case ACCEL_OPT_SGD: ps_apply_pull<OPT_SGD, 1><<<grid, 256, 0, s>>>(a); break;
-    case ACCEL_OPT_MOMENTUM: ps_apply_pull<OPT_MOMENTUM, 1><<<grid, 256, 0, s>>>(a); break;
-    default: ps_apply_pull<OPT_ADAM, 1><<<grid, 256, 0, s>>>(a); break;
-  }
-  ACCEL_CUDA(cudaGetLastError());
-  return ACCEL_OK;
+                           const float *grad_sumsq_dev, uint64_t sub_begin, uint64_t sub_count,
+                           uint32_t epoch, accel_stream_t stream) {
+  return do_apply_pull(ctx, peers, optimizer, slot0, slot1, n_contrib, hp, grad_sumsq_dev,
+                       sub_begin, sub_count, epoch, static_cast<cudaStream_t>(stream));
 }
 
-int accel_shard_wait_pull(accel_ctx *ctx, const accel_peers *peers, accel_stream_t stream) {
-  ShardArgs a;
-  int rc = fill_peers(peers, &a);
-  if (rc) return rc;
+int accel_shard_wait_pull(accel_ctx *ctx, const accel_peers *peers, uint32_t epoch,
+                          accel_stream_t stream) {
+  return do_wait_pull(ctx, peers, epoch, static_cast<cudaStream_t>(stream));
+}
+
+int accel_shard_step(accel_ctx *ctx, const accel_peers *peers, int optimizer, float *slot0,
+                     float *slot1, const void *const *grads, int n_workers, int grad_dtype,
+                     int n_contrib, const accel_hparams *hp, const float *grad_sumsq_dev,
+                     int n_chunks, accel_stream_t stream) {
+  if (!peers) return fail(ACCEL_ERR_INVALID, "peers is NULL");
+  if (n_chunks < 1 || n_chunks > 64)
+    return fail(ACCEL_ERR_INVALID, "n_chunks %d out of range [1,64]", n_chunks);
   TaskState *ts = nullptr;
-  rc = task_state(ctx, peers->rank, &ts);
+  int rc = task_state(ctx, peers->rank, &ts);
   if (rc) return rc;
-  if (ts->shard_epoch == 0)
-    return fail(ACCEL_ERR_STATE, "accel_shard_wait_pull before any accel_shard_push");
-  a.epoch = ts->shard_epoch;
-  ps_wait_pull<<<1, 32, 0, static_cast<cudaStream_t>(stream)>>>(a);
-  ACCEL_CUDA(cudaGetLastError());
-  return ACCEL_OK;
+  cudaStream_t s = static_cast<cudaStream_t>(stream);
+  if (!ts->shard_aux) {
+    ACCEL_CUDA(cudaStreamCreateWithFlags(&ts->shard_aux, cudaStreamNonBlocking));
+    ACCEL_CUDA(cudaEventCreateWithFlags(&ts->shard_ev_push, cudaEventDisableTiming));
+    ACCEL_CUDA(cudaEventCreateWithFlags(&ts->shard_ev_done, cudaEventDisableTiming));
+  }
+  // chunk = the same slice of every shard; slices are multiples of 8 elements
+  const uint64_t shard = peers->shard_elems;
+  uint64_t per = (shard / 8 + n_chunks - 1) / n_chunks * 8;
+  if (per == 0) per = 8;
+  uint32_t epoch = 0;
+  for (uint64_t begin = 0; begin < shard; begin += per) {
+    const uint64_t n = begin + per <= shard ? per : shard - begin;
+    // main stream: HBM-bound local sum + NVLink push of slice k ...
+    rc = do_push(ctx, peers, grads, n_workers, grad_dtype, begin, n, s, &epoch,
+                 n_chunks > 1 ? 1 : 2);
+    if (rc) return rc;
+    ACCEL_CUDA(cudaEventRecord(ts->shard_ev_push, s));
+    // ... while the auxiliary stream applies and broadcasts slice k-1 (NVLink-bound)
+    ACCEL_CUDA(cudaStreamWaitEvent(ts->shard_aux, ts->shard_ev_push, 0));
+    rc = do_apply_pull(ctx, peers, optimizer, slot0, slot1, n_contrib, hp, grad_sumsq_dev, begin,
+                       n, epoch, ts->shard_aux, n_chunks > 1 ? 2 : 4);
+    if (rc) return rc;
+  }
+  ACCEL_CUDA(cudaEventRecord(ts->shard_ev_done, ts->shard_aux));
+  ACCEL_CUDA(cudaStreamWaitEvent(s, ts->shard_ev_done, 0));
+  return do_wait_pull(ctx, peers, epoch, s);
 }
 
 int accel_shard_check(accel_ctx *ctx, const accel_peers *peers, accel_stream_t stream) {
   ShardArgs a;
-  int rc = fill_peers(peers, &a);
+  int rc = fill_peers(peers, 0, 0, &a);
   if (rc) return rc;
   TaskState *ts = nullptr;
   rc = task_state(ctx, peers->rank, &ts);
   if (rc) return rc;
   ACCEL_CUDA(cudaStreamSynchronize(static_cast<cudaStream_t>(stream)));
+  if (ts->shard_aux) ACCEL_CUDA(cudaStreamSynchronize(ts->shard_aux));
   uint32_t status = 0;
   ACCEL_CUDA(cudaMemcpy(&status, a.flags[a.rank] + kFlagStatus, sizeof(status),
                         cudaMemcpyDeviceToHost));

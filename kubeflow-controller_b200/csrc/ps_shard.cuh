@@ -1,0 +1,118 @@
+// Shared declarations of the multi-GPU PS step: argument block, flag layout, and the
+// cross-GPU signalling helpers. Included by ps_shard.cu (three-phase kernels) and
+// ps_shard_fused.cu (the one-kernel step).
+#pragma once
+
+#include <string.h>
+
+#include "ps_math.cuh"
+
+namespace accel {
+
+constexpr int kFlagPush = 0;     // [0,16): push of rank s has landed (epoch)
+constexpr int kFlagPull = 16;    // [16,32): apply_pull of rank s has landed
+constexpr int kFlagTicketPush = 32;
+constexpr int kFlagTicketApply = 33;
+constexpr int kFlagSliceTicket = 64;  // [64,128): per-slice tickets of the one-kernel step
+constexpr int kFlagStatus = 48;  // 0 ok, else error code | (waited-for rank << 8)
+constexpr unsigned long long kSpinTimeoutNs = 2000000000ull;  // 2 s
+
+struct ShardArgs {
+  float *stage[ACCEL_MAX_PS];
+  float *var[ACCEL_MAX_PS];
+  uint32_t *flags[ACCEL_MAX_PS];
+  const void *grad[ACCEL_MAX_WORKERS];
+  float *slot0;
+  float *slot1;
+  const float *sumsq;
+  float *var_mc;   // multicast mapping of all ranks' var replicas, or nullptr
+  uint64_t shard;  // elements per shard, multiple of 8
+  uint64_t sub_begin, sub_count;  // the slice of EVERY shard this launch covers (multiples of 8)
+  int rank, world, n_workers;
+  uint32_t epoch;
+  // optimizer scalars (see ApplyArgs)
+  int use_nesterov;
+  float lr, momentum, beta1, one_minus_beta1, one_minus_beta2, alpha, epsilon, mean_div, clip_norm;
+};
+
+__device__ __forceinline__ uint32_t ld_acquire_sys(const uint32_t *p) {
+  uint32_t v;
+  asm volatile("ld.acquire.sys.global.u32 %0, [%1];" : "=r"(v) : "l"(p) : "memory");
+  return v;
+}
+__device__ __forceinline__ void st_release_sys(uint32_t *p, uint32_t v) {
+  asm volatile("st.release.sys.global.u32 [%0], %1;" ::"l"(p), "r"(v) : "memory");
+}
+__device__ __forceinline__ unsigned long long globaltimer_ns() {
+  unsigned long long t;
+  asm volatile("mov.u64 %0, %globaltimer;" : "=l"(t));
+  return t;
+}
+
+// Thread 0 of the CTA waits until flags[base + s] has reached `epoch` for every
+// rank s. Returns false (for the whole CTA) on timeout or if another CTA
+// already recorded a failure.
+__device__ inline bool wait_all(uint32_t *flags, int base, int world, uint32_t epoch) {
+  __shared__ int ok;
+  if (threadIdx.x == 0) {
+    ok = 1;
+    const unsigned long long t0 = globaltimer_ns();
+    for (int s = 0; s < world && ok; ++s) {
+      // epochs only grow; signed distance handles the 32-bit wrap
+      while (static_cast<int32_t>(ld_acquire_sys(flags + base + s) - epoch) < 0) {
+        if (globaltimer_ns() - t0 > kSpinTimeoutNs || ld_acquire_sys(flags + kFlagStatus) != 0) {
+          atomicCAS(flags + kFlagStatus, 0u, 1u | (static_cast<uint32_t>(s) << 8) |
+                                                 (static_cast<uint32_t>(base) << 16));
+          ok = 0;
+          break;
+        }
+        __nanosleep(200);
+      }
+    }
+  }
+  __syncthreads();
+  return ok != 0;
+}
+
+// After the CTA's stores: the last CTA of the grid publishes `epoch` into word
+// [word_base + rank] of every rank's flags.
+__device__ inline void signal_all(const ShardArgs &a, int ticket_word, int word_base) {
+  __syncthreads();
+  if (threadIdx.x == 0) {
+    __threadfence_system();  // this CTA's peer stores are ordered before the ticket
+    uint32_t *local = a.flags[a.rank];
+    const unsigned int done = atomicAdd(local + ticket_word, 1u);
+    if (done == gridDim.x - 1) {
+      local[ticket_word] = 0;  // ready for the next launch
+      __threadfence_system();  // all CTAs' tickets (and their stores) happen-before the flags
+      for (int p = 0; p < a.world; ++p) st_release_sys(a.flags[p] + word_base + a.rank, a.epoch);
+    }
+  }
+}
+
+__device__ __forceinline__ void st_256(float *p, const float (&o)[8]) {
+  asm volatile("st.global.v8.f32 [%0], {%1,%2,%3,%4,%5,%6,%7,%8};" ::"l"(p), "f"(o[0]), "f"(o[1]),
+               "f"(o[2]), "f"(o[3]), "f"(o[4]), "f"(o[5]), "f"(o[6]), "f"(o[7])
+               : "memory");
+}
+__device__ __forceinline__ void st_multimem_128(float *mc, const float *o) {
+  asm volatile("multimem.st.weak.global.v4.f32 [%0], {%1,%2,%3,%4};" ::"l"(mc), "f"(o[0]),
+               "f"(o[1]), "f"(o[2]), "f"(o[3])
+               : "memory");
+}
+__device__ __forceinline__ void ld_256_plain(const float *p, float (&o)[8]) {
+  asm volatile("ld.global.L1::no_allocate.v8.f32 {%0,%1,%2,%3,%4,%5,%6,%7}, [%8];"
+               : "=f"(o[0]), "=f"(o[1]), "=f"(o[2]), "=f"(o[3]), "=f"(o[4]), "=f"(o[5]),
+                 "=f"(o[6]), "=f"(o[7])
+               : "l"(p)
+               : "memory");
+}
+
+
+// host side, defined in ps_shard.cu
+int fill_peers(const accel_peers *peers, uint64_t sub_begin, uint64_t sub_count, ShardArgs *a);
+int fill_optimizer(int optimizer, float *slot0, float *slot1, int n_contrib,
+                   const accel_hparams *hp, const float *grad_sumsq_dev, ShardArgs *a);
+int fill_grads(const void *const *grads, int n_workers, int grad_dtype, ShardArgs *a);
+
+}  // namespace accel

@@ -1,0 +1,339 @@
+// The multi-GPU PS step as ONE kernel per GPU (SURVEY §8 e): local N-way gradient sum +
+// reduce-scatter push, shard apply, all-gather pull, and the closing wait, overlapped
+// slice by slice over NVLink peer memory.
+//
+// Every CTA walks the slices in order. For slice k it (1) sums its part of the local
+// gradients and stores the partials into the owners' stage slots (peer stores are posted:
+// the SM moves on while NVLink drains), (2) takes a per-slice ticket — the last CTA
+// publishes "rank r pushed slice k" to every peer — and (3) without blocking, checks
+// whether earlier slices have arrived from ALL ranks and, if so, applies the optimizer to
+// its part of them and stores the new values into every replica. Only after its last push
+// does a CTA block (bounded) for the slices still missing. The last CTA to finish
+// publishes "rank r pulled" and waits (bounded) for the same from every peer, so kernel
+// completion = this rank's replica is complete.
+//
+// Progress: a CTA only ever BLOCKS after all of its own pushes are issued, and pushes never
+// wait, so every rank's push flags eventually arrive provided all CTAs of the grid are
+// resident — the launch is cooperative (co-residency guaranteed or the launch fails).
+//
+// R > 1 emulates R ranks that live on ONE GPU inside a single cooperative launch (CTA group
+// g plays rank g): the single-GPU test vehicle for the same code path.
+#include <cooperative_groups.h>
+
+#include "ps_shard.cuh"
+
+namespace accel {
+
+constexpr int kFusedThreads = 256;
+constexpr int kMaxSlices = 64;
+constexpr int kEmuRanks = 8;
+
+template <int R>
+struct FusedArgs {
+  ShardArgs r[R];
+  int ctas_per_rank;
+  int n_slices;
+  uint32_t epoch_base;  // slice k is published as epoch_base + k + 1, the pull as epoch_base + n_slices
+};
+
+// Non-blocking: have all ranks published >= target in words [base, base+world)?
+__device__ inline bool poll_all(uint32_t *flags, int base, int world, uint32_t target) {
+  __shared__ int ready;
+  if (threadIdx.x == 0) {
+    int ok = 1;
+    for (int s = 0; s < world; ++s)
+      ok &= static_cast<int32_t>(ld_acquire_sys(flags + base + s) - target) >= 0;
+    ready = ok;
+  }
+  __syncthreads();
+  const bool r = ready != 0;
+  __syncthreads();  // `ready` may be rewritten by the next poll
+  return r;
+}
+
+template <typename G, int NW>
+__device__ __forceinline__ void push_slice(const ShardArgs &a, uint64_t sub_first,
+                                           uint64_t sub_items, int bid, int nb) {
+  const uint64_t shard_items = a.shard / 8;
+  const uint64_t n_items = sub_items * a.world;
+  const int n = NW > 0 ? NW : a.n_workers;
+  for (uint64_t l = static_cast<uint64_t>(bid) * blockDim.x + threadIdx.x; l < n_items;
+       l += static_cast<uint64_t>(nb) * blockDim.x) {
+    const uint64_t k = l / sub_items;
+    int c = a.rank + 1 + static_cast<int>(k);  // rotation: start with the right-hand neighbour
+    if (c >= a.world) c -= a.world;
+    const uint64_t within = sub_first + (l - k * sub_items);
+    const uint64_t item = static_cast<uint64_t>(c) * shard_items + within;
+    float acc[8];
+    if constexpr (NW > 0) {
+      float g[NW][8];
+#pragma unroll
+      for (int w = 0; w < NW; ++w) load_grad_item<G, true>(a.grad[w], item, g[w]);
+#pragma unroll
+      for (int e = 0; e < 8; ++e) {
+        acc[e] = g[0][e];
+#pragma unroll
+        for (int w = 1; w < NW; ++w) acc[e] = __fadd_rn(acc[e], g[w][e]);
+      }
+    } else {
+      load_grad_item<G, true>(a.grad[0], item, acc);
+      for (int w0 = 1; w0 < n; w0 += 4) {
+        float g[4][8];
+#pragma unroll
+        for (int q = 0; q < 4; ++q)
+          if (w0 + q < n) load_grad_item<G, true>(a.grad[w0 + q], item, g[q]);
+#pragma unroll
+        for (int q = 0; q < 4; ++q)
+          if (w0 + q < n)
+#pragma unroll
+            for (int e = 0; e < 8; ++e) acc[e] = __fadd_rn(acc[e], g[q][e]);
+      }
+    }
+    st_256(a.stage[c] + (static_cast<uint64_t>(a.rank) * shard_items + within) * 8, acc);
+  }
+}
+
+template <int OPT>
+__device__ __forceinline__ void apply_slice(const ShardArgs &a, const Scalars &sc,
+                                            uint64_t sub_first, uint64_t sub_items, int bid,
+                                            int nb) {
+  constexpr int SLOTS = OptTraits<OPT>::kSlots;
+  const uint64_t shard_items = a.shard / 8;
+  const float *stage = a.stage[a.rank];
+  const uint64_t var_off = static_cast<uint64_t>(a.rank) * a.shard;
+  for (uint64_t i = static_cast<uint64_t>(bid) * blockDim.x + threadIdx.x; i < sub_items;
+       i += static_cast<uint64_t>(nb) * blockDim.x) {
+    const uint64_t it = sub_first + i;
+    float acc[8], v[8], s0[8], s1[8];
+    ld_state_256(a.var[a.rank] + var_off + it * 8, v);
+    if constexpr (SLOTS >= 1) ld_state_256(a.slot0 + it * 8, s0);
+    if constexpr (SLOTS >= 2) ld_state_256(a.slot1 + it * 8, s1);
+    for (int s0i = 0; s0i < a.world; s0i += 4) {
+      float g[4][8];
+#pragma unroll
+      for (int q = 0; q < 4; ++q)
+        if (s0i + q < a.world)
+          ld_256_plain(stage + (static_cast<uint64_t>(s0i + q) * shard_items + it) * 8, g[q]);
+#pragma unroll
+      for (int q = 0; q < 4; ++q)
+        if (s0i + q < a.world)
+#pragma unroll
+          for (int e = 0; e < 8; ++e) acc[e] = (s0i + q == 0) ? g[q][e] : __fadd_rn(acc[e], g[q][e]);
+    }
+#pragma unroll
+    for (int e = 0; e < 8; ++e) update<OPT>(v[e], s0[e], s1[e], finish_grad(acc[e], sc), sc);
+    if constexpr (SLOTS >= 1) st_state_256(a.slot0 + it * 8, s0);
+    if constexpr (SLOTS >= 2) st_state_256(a.slot1 + it * 8, s1);
+    for (int q = 0; q < a.world; ++q) {
+      int p = a.rank + q;
+      if (p >= a.world) p -= a.world;
+      st_256(a.var[p] + var_off + it * 8, v);
+    }
+  }
+}
+
+template <typename G, int NW, int OPT, int R>
+__global__ void __launch_bounds__(kFusedThreads, 2)
+    ps_step_fused(const __grid_constant__ FusedArgs<R> fa) {
+  const int vr = R == 1 ? 0 : blockIdx.x / fa.ctas_per_rank;
+  const ShardArgs &a = fa.r[vr];
+  const int nb = fa.ctas_per_rank;
+  const int bid = R == 1 ? blockIdx.x : blockIdx.x - vr * nb;
+  uint32_t *flags = a.flags[a.rank];
+
+  ApplyArgs sa;  // scalars only
+  sa.sumsq = a.sumsq;
+  sa.use_nesterov = a.use_nesterov;
+  sa.lr = a.lr;
+  sa.momentum = a.momentum;
+  sa.beta1 = a.beta1;
+  sa.one_minus_beta1 = a.one_minus_beta1;
+  sa.one_minus_beta2 = a.one_minus_beta2;
+  sa.alpha = a.alpha;
+  sa.epsilon = a.epsilon;
+  sa.mean_div = a.mean_div;
+  sa.clip_norm = a.clip_norm;
+  const Scalars sc = make_scalars(sa);
+
+  const uint64_t shard_items = a.shard / 8;
+  const int S = fa.n_slices;
+  const uint64_t per = (shard_items + S - 1) / S;
+  auto slice_first = [&](int k) { return per * k < shard_items ? per * k : shard_items; };
+  auto slice_items = [&](int k) {
+    const uint64_t f = slice_first(k);
+    return f + per <= shard_items ? per : shard_items - f;
+  };
+
+  int next_apply = 0;
+  for (int k = 0; k < S; ++k) {
+    push_slice<G, NW>(a, slice_first(k), slice_items(k), bid, nb);
+    // per-slice ticket: the last CTA of this rank publishes slice k to every rank
+    __syncthreads();
+    if (threadIdx.x == 0) {
+      __threadfence_system();
+      const unsigned int done = atomicAdd(flags + kFlagSliceTicket + k, 1u);
+      if (done == static_cast<unsigned int>(nb) - 1) {
+        flags[kFlagSliceTicket + k] = 0;
+        __threadfence_system();
+        for (int p = 0; p < a.world; ++p)
+          st_release_sys(a.flags[p] + kFlagPush + a.rank, fa.epoch_base + k + 1);
+      }
+    }
+    // whatever has already arrived from everybody gets applied now, without waiting
+    while (next_apply < k && poll_all(flags, kFlagPush, a.world, fa.epoch_base + next_apply + 1)) {
+      apply_slice<OPT>(a, sc, slice_first(next_apply), slice_items(next_apply), bid, nb);
+      ++next_apply;
+    }
+  }
+  // all pushes of this CTA are issued: now it may block for what is still missing
+  for (; next_apply < S; ++next_apply) {
+    if (!wait_all(flags, kFlagPush, a.world, fa.epoch_base + next_apply + 1)) return;
+    apply_slice<OPT>(a, sc, slice_first(next_apply), slice_items(next_apply), bid, nb);
+  }
+  // pull signal, then the closing wait by the CTA that took the last ticket
+  __syncthreads();
+  __shared__ int last;
+  if (threadIdx.x == 0) {
+    __threadfence_system();
+    const unsigned int done = atomicAdd(flags + kFlagTicketApply, 1u);
+    last = done == static_cast<unsigned int>(nb) - 1;
+    if (last) {
+      flags[kFlagTicketApply] = 0;
+      __threadfence_system();
+      for (int p = 0; p < a.world; ++p)
+        st_release_sys(a.flags[p] + kFlagPull + a.rank, fa.epoch_base + S);
+    }
+  }
+  __syncthreads();
+  if (last) wait_all(flags, kFlagPull, a.world, fa.epoch_base + S);
+}
+
+template <typename G, int NW, int OPT, int R>
+static int launch_fused_one(const FusedArgs<R> &fa_in, int n_ranks, const TaskState &ts,
+                            int ctas_per_sm_cap, cudaStream_t s) {
+  auto kern = ps_step_fused<G, NW, OPT, R>;
+  int per_sm = 0;
+  ACCEL_CUDA(cudaOccupancyMaxActiveBlocksPerMultiprocessor(&per_sm, kern, kFusedThreads, 0));
+  if (per_sm < 1) return fail(ACCEL_ERR_CUDA, "fused step kernel does not fit on an SM");
+  if (per_sm > ctas_per_sm_cap) per_sm = ctas_per_sm_cap;
+  FusedArgs<R> fa = fa_in;
+  const int resident = per_sm * ts.sm_count;
+  fa.ctas_per_rank = resident / n_ranks;
+  if (fa.ctas_per_rank < 1)
+    return fail(ACCEL_ERR_INVALID, "%d ranks do not fit in %d resident CTAs", n_ranks, resident);
+  void *params[] = {&fa};
+  ACCEL_CUDA(cudaLaunchCooperativeKernel(reinterpret_cast<void *>(kern),
+                                         dim3(fa.ctas_per_rank * n_ranks), dim3(kFusedThreads),
+                                         params, 0, s));
+  return ACCEL_OK;
+}
+
+template <typename G, int OPT, int R>
+static int launch_fused_nw(const FusedArgs<R> &fa, int n_ranks, const TaskState &ts, int cap,
+                           cudaStream_t s) {
+  switch (fa.r[0].n_workers) {
+    case 1: return launch_fused_one<G, 1, OPT, R>(fa, n_ranks, ts, cap, s);
+    case 2: return launch_fused_one<G, 2, OPT, R>(fa, n_ranks, ts, cap, s);
+    case 4: return launch_fused_one<G, 4, OPT, R>(fa, n_ranks, ts, cap, s);
+    case 8: return launch_fused_one<G, 8, OPT, R>(fa, n_ranks, ts, cap, s);
+    default: return launch_fused_one<G, 0, OPT, R>(fa, n_ranks, ts, cap, s);
+  }
+}
+
+template <int R>
+static int launch_fused(const FusedArgs<R> &fa, int n_ranks, int optimizer, int grad_dtype,
+                        const TaskState &ts, int cap, cudaStream_t s) {
+  const bool bf = grad_dtype == ACCEL_BF16;
+  switch (optimizer) {
+    case ACCEL_OPT_SGD:
+      return bf ? launch_fused_nw<bf16_t, OPT_SGD, R>(fa, n_ranks, ts, cap, s)
+                : launch_fused_nw<float, OPT_SGD, R>(fa, n_ranks, ts, cap, s);
+    case ACCEL_OPT_MOMENTUM:
+      return bf ? launch_fused_nw<bf16_t, OPT_MOMENTUM, R>(fa, n_ranks, ts, cap, s)
+                : launch_fused_nw<float, OPT_MOMENTUM, R>(fa, n_ranks, ts, cap, s);
+    default:
+      return bf ? launch_fused_nw<bf16_t, OPT_ADAM, R>(fa, n_ranks, ts, cap, s)
+                : launch_fused_nw<float, OPT_ADAM, R>(fa, n_ranks, ts, cap, s);
+  }
+}
+
+static int fill_rank(const accel_peers *peers, int optimizer, float *slot0, float *slot1,
+                     const void *const *grads, int n_workers, int grad_dtype, int n_contrib,
+                     const accel_hparams *hp, const float *sumsq, ShardArgs *a) {
+  int rc = fill_peers(peers, 0, 0, a);
+  if (rc) return rc;
+  rc = fill_grads(grads, n_workers, grad_dtype, a);
+  if (rc) return rc;
+  return fill_optimizer(optimizer, slot0, slot1, n_contrib, hp, sumsq, a);
+}
+
+static int clamp_slices(int n_slices, uint64_t shard_elems) {
+  if (n_slices < 1) n_slices = 1;
+  if (n_slices > kMaxSlices) n_slices = kMaxSlices;
+  const uint64_t items = shard_elems / 8;
+  if (static_cast<uint64_t>(n_slices) > items) n_slices = static_cast<int>(items);
+  return n_slices;
+}
+
+}  // namespace accel
+
+using namespace accel;
+
+extern "C" {
+
+int accel_shard_step_fused(accel_ctx *ctx, const accel_peers *peers, int optimizer, float *slot0,
+                           float *slot1, const void *const *grads, int n_workers, int grad_dtype,
+                           int n_contrib, const accel_hparams *hp, const float *grad_sumsq_dev,
+                           int n_slices, accel_stream_t stream) {
+  if (!peers) return fail(ACCEL_ERR_INVALID, "peers is NULL");
+  TaskState *ts = nullptr;
+  int rc = task_state(ctx, peers->rank, &ts);
+  if (rc) return rc;
+  FusedArgs<1> fa;
+  rc = fill_rank(peers, optimizer, slot0, slot1, grads, n_workers, grad_dtype, n_contrib, hp,
+                 grad_sumsq_dev, &fa.r[0]);
+  if (rc) return rc;
+  fa.n_slices = clamp_slices(n_slices, peers->shard_elems);
+  fa.epoch_base = ts->shard_epoch;
+  ts->shard_epoch += fa.n_slices;
+  fa.ctas_per_rank = 0;
+  return launch_fused<1>(fa, 1, optimizer, grad_dtype, *ts, 2, static_cast<cudaStream_t>(stream));
+}
+
+int accel_shard_step_local_group(accel_ctx *ctx, const accel_peers *const *peers_of_rank,
+                                 int n_ranks, int optimizer, float *const *slot0,
+                                 float *const *slot1, const void *const *const *grads,
+                                 int n_workers, int grad_dtype, int n_contrib,
+                                 const accel_hparams *hp, const float *grad_sumsq_dev,
+                                 int n_slices, accel_stream_t stream) {
+  if (!peers_of_rank || !grads) return fail(ACCEL_ERR_INVALID, "peers_of_rank/grads is NULL");
+  if (n_ranks < 1 || n_ranks > kEmuRanks)
+    return fail(ACCEL_ERR_INVALID, "n_ranks %d out of range [1,%d]", n_ranks, kEmuRanks);
+  FusedArgs<kEmuRanks> fa;
+  memset(&fa, 0, sizeof(fa));
+  TaskState *ts0 = nullptr;
+  for (int r = 0; r < n_ranks; ++r) {
+    if (!peers_of_rank[r]) return fail(ACCEL_ERR_INVALID, "peers_of_rank[%d] is NULL", r);
+    if (peers_of_rank[r]->rank != r || peers_of_rank[r]->world != n_ranks)
+      return fail(ACCEL_ERR_INVALID, "peers_of_rank[%d] must describe rank %d of %d", r, r, n_ranks);
+    TaskState *ts = nullptr;
+    int rc = task_state(ctx, r, &ts);
+    if (rc) return rc;
+    if (r == 0) ts0 = ts;
+    if (ts->device != ts0->device)
+      return fail(ACCEL_ERR_INVALID, "a local group lives on one GPU; rank %d is on another", r);
+    if (ts->shard_epoch != ts0->shard_epoch)
+      return fail(ACCEL_ERR_STATE, "ranks of a local group must be in the same epoch");
+    rc = fill_rank(peers_of_rank[r], optimizer, slot0 ? slot0[r] : nullptr,
+                   slot1 ? slot1[r] : nullptr, grads[r], n_workers, grad_dtype, n_contrib, hp,
+                   grad_sumsq_dev, &fa.r[r]);
+    if (rc) return rc;
+  }
+  fa.n_slices = clamp_slices(n_slices, peers_of_rank[0]->shard_elems);
+  fa.epoch_base = ts0->shard_epoch;
+  for (int r = 0; r < n_ranks; ++r) ctx->task[r].shard_epoch += fa.n_slices;
+  return launch_fused<kEmuRanks>(fa, n_ranks, optimizer, grad_dtype, *ts0, 2,
+                                 static_cast<cudaStream_t>(stream));
+}
+
+}  // extern "C"

@@ -3,12 +3,16 @@ task_index r = GPU r = rank r = shard r of the flat arena (SURVEY §8 e).
 
 A step is push -> apply_pull -> wait_pull (csrc/ps_shard.cu): the worker->PS push
 is a reduce-scatter fused into the local gradient sum, the PS->worker pull an
-all-gather fused into the optimizer apply, both as peer stores over NVLink.
-`mode="nccl"` runs the same step with NCCL's reduce-scatter / all-gather around
-the library's kernels — the baseline the fused path is measured against.
+all-gather fused into the optimizer apply, both as stores over NVLink (unicast
+peer stores, or one multicast store through the NVSwitch when a multicast mapping
+is available). `accel_shard_step` cuts the arena into slices and overlaps the
+push of slice k+1 with the apply_pull of slice k. `mode="nccl"` runs the same
+step with NCCL's reduce-scatter / all-gather around the library's kernels — the
+baseline the fused path is measured against.
 
-torch.distributed is used only for the rendezvous (exchange of IPC handles) and,
-in nccl mode, for the two collectives.
+torch.distributed is plumbing only: the rendezvous (exchange of CUDA IPC handles,
+or torch's symmetric-memory allocator, which also yields the multicast mapping)
+and, in nccl mode, the two collectives.
 """
 from __future__ import annotations
 
@@ -76,13 +80,46 @@ def exchange(obj, world: int):
     return out
 
 
+class SymmBuffer:
+    """A buffer from torch's symmetric-memory allocator, rendezvoused over the default
+    process group: peers' addresses plus (when the fabric supports it) a multicast address."""
+
+    def __init__(self, nbytes: int, device_index: int):
+        import torch.distributed as dist
+        import torch.distributed._symmetric_memory as symm
+        self.nbytes, self.device_index = nbytes, device_index
+        dev = torch.device("cuda", device_index)
+        group = dist.group.WORLD
+        symm.enable_symm_mem_for_group(group.group_name)
+        self._t = symm.empty(nbytes // 4, dtype=torch.float32, device=dev)
+        self._t.zero_()
+        self.handle = symm.rendezvous(self._t, group)
+        self.ptr = self._t.data_ptr()
+        self.peer_ptrs = [int(p) for p in self.handle.buffer_ptrs]
+        mc = getattr(self.handle, "multicast_ptr", 0)
+        self.multicast_ptr = int(mc) if mc else 0
+
+    def tensor(self, dtype=torch.float32) -> torch.Tensor:
+        return self._t if dtype == torch.float32 else self._t.view(dtype)
+
+    def free(self):
+        self._t = None
+
+
 class ShardedPS:
     def __init__(self, rank: int, world: int, device_index: int, elems: int, optimizer: int,
                  hp: accel.HParams, mode: str = "fused", ctx: accel.Context | None = None,
-                 peer_ptrs=None, gpu_ordinals=None):
-        if mode not in ("fused", "nccl"):
+                 peer_ptrs=None, gpu_ordinals=None, n_chunks: int | None = None,
+                 rendezvous: str = "ipc", multicast: bool = False):
+        if mode not in ("fused", "streams", "nccl"):
             raise ValueError(f"unknown mode {mode!r}")
+        if rendezvous not in ("ipc", "symm"):
+            raise ValueError(f"unknown rendezvous {rendezvous!r}")
         self.rank, self.world, self.mode = rank, world, mode
+        # slices of the step: measured on B200, overlap pays at 2 ranks (4 slices: 0.817 ms vs
+        # 0.874 ms) and costs at 8 (1 slice: 1.166 ms, 2: 1.184 ms, 4: 1.299 ms)
+        self.n_chunks = n_chunks or (4 if world <= 2 else 2 if world <= 4 else 1)
+        self.multicast_ptr = 0
         self.device_index = device_index
         self.device = torch.device("cuda", device_index)
         self.optimizer, self.hp = optimizer, hp
@@ -94,9 +131,18 @@ class ShardedPS:
         self.lib = accel.load_library()
         self.global_step = 0
         # exportable buffers: full variable replica, receive slots, flag words
-        self.buf_var = DevBuffer(self.padded * 4, device_index)
-        self.buf_stage = DevBuffer(self.padded * 4, device_index)
-        self.buf_flags = DevBuffer(256, device_index)
+        if rendezvous == "symm" and peer_ptrs is None:
+            self.buf_var = SymmBuffer(self.padded * 4, device_index)
+            self.buf_stage = SymmBuffer(self.padded * 4, device_index)
+            self.buf_flags = SymmBuffer(1024, device_index)
+            peer_ptrs = list(zip(self.buf_var.peer_ptrs, self.buf_stage.peer_ptrs,
+                                 self.buf_flags.peer_ptrs))
+            if multicast:
+                self.multicast_ptr = self.buf_var.multicast_ptr
+        else:
+            self.buf_var = DevBuffer(self.padded * 4, device_index)
+            self.buf_stage = DevBuffer(self.padded * 4, device_index)
+            self.buf_flags = DevBuffer(1024, device_index)
         self.var = self.buf_var.tensor()
         self.stage = self.buf_stage.tensor()
         self.flags = self.buf_flags.tensor(torch.int32)
@@ -106,7 +152,8 @@ class ShardedPS:
             self.slot1 = torch.zeros(self.shard, device=self.device) \
                 if optimizer == accel.OPT_ADAM else None
             self.gshard = torch.empty(self.shard, device=self.device) if mode == "nccl" else None
-        self.launches_per_step = 3 if mode == "fused" else 2
+        n_slices = -(-(self.shard // 8) // (-(-(self.shard // 8) // self.n_chunks)))
+        self.launches_per_step = {"fused": 1, "streams": 2 * n_slices + 1, "nccl": 2}[mode]
         if peer_ptrs is None:
             mine = (self.buf_var.export(), self.buf_stage.export(), self.buf_flags.export())
             handles = exchange(mine, world)
@@ -126,34 +173,43 @@ class ShardedPS:
         self._stage_arr = (ctypes.c_void_p * w)(*[p[1] for p in peer_ptrs])
         self._flags_arr = (ctypes.c_void_p * w)(*[p[2] for p in peer_ptrs])
         self.peers = accel.Peers(self.rank, w, self.shard, self._stage_arr, self._var_arr,
-                                 self._flags_arr)
+                                 self._flags_arr, self.multicast_ptr or None)
         # world = 1 view onto the same stage buffer: the local pre-sum of nccl mode
         self._solo_var = (ctypes.c_void_p * 1)(self.buf_var.ptr)
         self._solo_stage = (ctypes.c_void_p * 1)(self.buf_stage.ptr)
         self._solo_flags = (ctypes.c_void_p * 1)(self.buf_flags.ptr)
         self.solo = accel.Peers(0, 1, self.padded, self._solo_stage, self._solo_var,
-                                self._solo_flags)
+                                self._solo_flags, None)
 
     @property
     def var_shard(self) -> torch.Tensor:
         return self.var[self.rank * self.shard:(self.rank + 1) * self.shard]
 
     # ---- the three phases (exposed so a single GPU can emulate several ranks in turn) ----
-    def push(self, grads, stream=None, peers=None):
+    def push(self, grads, stream=None, peers=None, sub=(0, 0)) -> int:
+        """Returns the epoch this push opened."""
         ctx = self.solo_ctx if peers is self.solo else self.ctx
+        epoch = ctypes.c_uint32()
         accel.check(self.lib.accel_shard_push(
             ctx.handle, ctypes.byref(peers or self.peers), accel._grad_array(grads),
-            len(grads), accel._grad_dtype(grads[0]), accel._stream_handle(stream)))
+            len(grads), accel._grad_dtype(grads[0]), sub[0], sub[1],
+            accel._stream_handle(stream), ctypes.byref(epoch)))
+        return epoch.value
 
-    def apply_pull(self, n_contrib: int, sumsq=None, stream=None):
+    def apply_pull(self, n_contrib: int, sumsq=None, stream=None, sub=(0, 0), epoch=0):
         accel.check(self.lib.accel_shard_apply_pull(
             self.ctx.handle, ctypes.byref(self.peers), self.optimizer, accel._ptr(self.slot0),
             accel._ptr(self.slot1), n_contrib, ctypes.byref(self.hp), accel._ptr(sumsq),
-            accel._stream_handle(stream)))
+            sub[0], sub[1], epoch, accel._stream_handle(stream)))
 
-    def wait_pull(self, stream=None):
+    def wait_pull(self, stream=None, epoch=0):
         accel.check(self.lib.accel_shard_wait_pull(self.ctx.handle, ctypes.byref(self.peers),
-                                                   accel._stream_handle(stream)))
+                                                   epoch, accel._stream_handle(stream)))
+
+    def slices(self):
+        """The (begin, count) slices accel_shard_step cuts every shard into."""
+        per = -(-(self.shard // 8) // self.n_chunks) * 8
+        return [(b, min(per, self.shard - b)) for b in range(0, self.shard, per)]
 
     def check(self, stream=None):
         """Synchronise and raise if a cross-GPU wait of this rank timed out."""
@@ -168,10 +224,14 @@ class ShardedPS:
     def step(self, grads, stream=None, sumsq=None):
         """grads: this rank's local worker gradients, each `padded` elements."""
         n_contrib = len(grads) * self.world
-        if self.mode == "fused":
-            self.push(grads, stream)
-            self.apply_pull(n_contrib, sumsq, stream)
-            self.wait_pull(stream)
+        if self.mode in ("fused", "streams"):
+            fn = self.lib.accel_shard_step_fused if self.mode == "fused" \
+                else self.lib.accel_shard_step
+            accel.check(fn(
+                self.ctx.handle, ctypes.byref(self.peers), self.optimizer,
+                accel._ptr(self.slot0), accel._ptr(self.slot1), accel._grad_array(grads),
+                len(grads), accel._grad_dtype(grads[0]), n_contrib, ctypes.byref(self.hp),
+                accel._ptr(sumsq), self.n_chunks, accel._stream_handle(stream)))
         else:
             import torch.distributed as dist
             if self.hp.aggregate != accel.AGG_SUM:
@@ -184,7 +244,8 @@ class ShardedPS:
         self.finish_step()
 
 
-def local_group(world: int, elems: int, optimizer: int, hp_factory, device_index: int = 0):
+def local_group(world: int, elems: int, optimizer: int, hp_factory, device_index: int = 0,
+                n_chunks: int = 1):
     """`world` ranks emulated on ONE GPU inside one process (tests): every rank's buffers are
     plain local allocations and the phases are run rank after rank on one stream, so every
     device-side wait is already satisfied when its kernel starts."""
@@ -192,7 +253,7 @@ def local_group(world: int, elems: int, optimizer: int, hp_factory, device_index
     ranks = []
     for r in range(world):
         ranks.append(ShardedPS(r, world, device_index, elems, optimizer, hp_factory(), ctx=ctx,
-                               peer_ptrs=[(0, 0, 0)] * world))
+                               peer_ptrs=[(0, 0, 0)] * world, n_chunks=n_chunks))
     ptrs = [(x.buf_var.ptr, x.buf_stage.ptr, x.buf_flags.ptr) for x in ranks]
     for x in ranks:
         x.set_peers(ptrs)
@@ -200,13 +261,41 @@ def local_group(world: int, elems: int, optimizer: int, hp_factory, device_index
 
 
 def local_group_step(ranks, grads_per_rank, stream=None, sumsq=None):
+    """One step of the emulated group, slice by slice and phase by phase: all ranks push slice
+    k, then all ranks apply_pull slice k (its waits are already satisfied), as the pipelined
+    accel_shard_step orders them on real peers."""
     n_contrib = sum(len(g) for g in grads_per_rank)
-    for x, g in zip(ranks, grads_per_rank):
-        x.push(g, stream)
+    epoch = 0
+    for sub in ranks[0].slices():
+        epochs = [x.push(g, stream, sub=sub) for x, g in zip(ranks, grads_per_rank)]
+        assert len(set(epochs)) == 1, "ranks must advance their epochs in lock step"
+        epoch = epochs[0]
+        for x in ranks:
+            x.apply_pull(n_contrib, sumsq, stream, sub=sub, epoch=epoch)
     for x in ranks:
-        x.apply_pull(n_contrib, sumsq, stream)
+        x.wait_pull(stream, epoch=epoch)
     for x in ranks:
-        x.wait_pull(stream)
+        x.check(stream)
+        x.finish_step()
+
+
+def local_group_step_fused(ranks, grads_per_rank, n_slices=None, stream=None, sumsq=None):
+    """One step of the emulated group through the ONE-kernel path: a single cooperative
+    launch plays every rank (accel_shard_step_local_group)."""
+    n = len(ranks)
+    x0 = ranks[0]
+    n_contrib = sum(len(g) for g in grads_per_rank)
+    PP = ctypes.POINTER(accel.Peers)
+    peers = (PP * n)(*[ctypes.pointer(x.peers) for x in ranks])
+    s0 = (ctypes.c_void_p * n)(*[accel._ptr(x.slot0) for x in ranks])
+    s1 = (ctypes.c_void_p * n)(*[accel._ptr(x.slot1) for x in ranks])
+    garr = [accel._grad_array(g) for g in grads_per_rank]
+    pvp = ctypes.POINTER(ctypes.c_void_p)
+    gg = (pvp * n)(*[ctypes.cast(a, pvp) for a in garr])
+    accel.check(x0.lib.accel_shard_step_local_group(
+        x0.ctx.handle, peers, n, x0.optimizer, s0, s1, gg, len(grads_per_rank[0]),
+        accel._grad_dtype(grads_per_rank[0][0]), n_contrib, ctypes.byref(x0.hp),
+        accel._ptr(sumsq), n_slices or x0.n_chunks, accel._stream_handle(stream)))
     for x in ranks:
         x.check(stream)
         x.finish_step()

@@ -31,15 +31,17 @@ def _oracle_hier(grads_per_rank, mean):
     return total
 
 
-@pytest.mark.parametrize("world", [1, 2, 4, 8])
+@pytest.mark.parametrize("world,chunks", [(1, 1), (2, 1), (2, 3), (4, 4), (8, 1), (8, 5)])
 @pytest.mark.parametrize("opt", [O.SGD, O.MOMENTUM, O.ADAM])
 @pytest.mark.parametrize("workers,bf16,mean", [(1, False, False), (8, False, True), (3, True, True)])
-def test_sharded_step_matches_oracle(pkg, world, opt, workers, bf16, mean):
+def test_sharded_step_matches_oracle(pkg, world, chunks, opt, workers, bf16, mean):
     from kubeflow_controller_b200 import sharded
     elems = 100_003
     agg = pkg.AGG_MEAN if mean else pkg.AGG_SUM
     ranks = sharded.local_group(world, elems, opt,
-                                lambda: pkg.HParams(lr=0.01, momentum=0.9, aggregate=agg))
+                                lambda: pkg.HParams(lr=0.01, momentum=0.9, aggregate=agg),
+                                n_chunks=chunks)
+    assert sum(n for _, n in ranks[0].slices()) == ranks[0].shard
     padded, shard = ranks[0].padded, ranks[0].shard
     assert padded % (8 * world) == 0 and padded >= elems
     rng = np.random.default_rng(world * 10 + workers)
@@ -110,6 +112,79 @@ def test_shard_argument_errors(pkg):
         x.wait_pull()
     with pytest.raises(pkg.AccelError, match="aligned"):
         x.push([torch.ones(x.padded + 1, device=DEV)[1:]])
-    bad = pkg.accel.Peers(0, 2, 12, x._stage_arr, x._var_arr, x._flags_arr)
+    bad = pkg.accel.Peers(0, 2, 12, x._stage_arr, x._var_arr, x._flags_arr, None)
     with pytest.raises(pkg.AccelError, match="multiple of 8"):
         x.push([torch.ones(x.padded, device=DEV)], peers=bad)
+    with pytest.raises(pkg.AccelError, match="sub-range"):
+        x.push([torch.ones(x.padded, device=DEV)], sub=(8, x.shard))
+    with pytest.raises(pkg.AccelError, match="sub-range"):
+        x.push([torch.ones(x.padded, device=DEV)], sub=(4, 8))
+
+
+def test_single_rank_pipelined_step_call(pkg):
+    """accel_shard_step itself (two streams, slices) with a world of one: no peer to wait for."""
+    from kubeflow_controller_b200 import sharded
+    n = 300_000
+    x = sharded.local_group(1, n, pkg.OPT_MOMENTUM,
+                            lambda: pkg.HParams(lr=0.1, momentum=0.9), n_chunks=3)[0]
+    rng = np.random.default_rng(1)
+    var = rng.standard_normal(x.padded).astype(F)
+    acc = np.zeros(x.padded, F)
+    x.var.copy_(_dev(var))
+    for _ in range(3):
+        g = [(0.01 * rng.standard_normal(x.padded)).astype(F) for _ in range(2)]
+        x.step([_dev(a) for a in g])
+        O.numpy_ps_step(O.MOMENTUM, var, acc, None, g, O.HParams(lr=0.1, momentum=0.9))
+    x.check()
+    assert np.array_equal(x.var.cpu().numpy(), var)
+    assert np.array_equal(x.slot0.cpu().numpy(), acc)
+
+
+@pytest.mark.parametrize("world,slices", [(1, 1), (2, 1), (2, 4), (4, 7), (8, 16), (8, 64)])
+@pytest.mark.parametrize("opt", [O.SGD, O.MOMENTUM, O.ADAM])
+@pytest.mark.parametrize("workers,bf16,mean", [(1, False, False), (8, False, True), (5, True, True)])
+def test_one_kernel_step_matches_oracle(pkg, world, slices, opt, workers, bf16, mean):
+    """The ONE-kernel step (push, apply, pull and closing wait overlapped inside a cooperative
+    launch), all ranks played by one launch on this GPU: bit-exact against the oracle."""
+    from kubeflow_controller_b200 import sharded
+    elems = 100_003
+    agg = pkg.AGG_MEAN if mean else pkg.AGG_SUM
+    ranks = sharded.local_group(world, elems, opt,
+                                lambda: pkg.HParams(lr=0.01, momentum=0.9, aggregate=agg))
+    padded, shard = ranks[0].padded, ranks[0].shard
+    rng = np.random.default_rng(world * 100 + slices)
+    var = rng.standard_normal(padded).astype(F)
+    s0, s1 = np.zeros(padded, F), np.zeros(padded, F)
+    for x in ranks:
+        x.var.copy_(_dev(var))
+    ohp = O.HParams(lr=0.01, momentum=0.9)
+    for step in range(3):
+        gpr = []
+        for r in range(world):
+            g = [(0.01 * rng.standard_normal(padded)).astype(F) for _ in range(workers)]
+            if bf16:
+                g = [O.f32_to_bf16_bits(x) for x in g]
+            gpr.append(g)
+        sharded.local_group_step_fused(ranks, [[_dev(g) for g in gr] for gr in gpr],
+                                       n_slices=slices)
+        O.numpy_apply(opt, var, s0, s1, _oracle_hier(gpr, mean), ohp)
+        ohp.advance()
+    torch.cuda.synchronize()
+    for x in ranks:
+        assert np.array_equal(x.var.cpu().numpy(), var), f"rank {x.rank} replica differs"
+        lo = x.rank * shard
+        if opt >= O.MOMENTUM:
+            assert np.array_equal(x.slot0.cpu().numpy(), s0[lo:lo + shard])
+        if opt == O.ADAM:
+            assert np.array_equal(x.slot1.cpu().numpy(), s1[lo:lo + shard])
+
+
+def test_one_kernel_step_then_three_phase_step_share_epochs(pkg):
+    """Both step forms advance the same epoch counter, so they can be mixed."""
+    from kubeflow_controller_b200 import sharded
+    ranks = sharded.local_group(2, 40_000, pkg.OPT_SGD, lambda: pkg.HParams(lr=1.0))
+    g = [[torch.ones(ranks[0].padded, device=DEV)] for _ in ranks]
+    sharded.local_group_step_fused(ranks, g, n_slices=3)
+    sharded.local_group_step(ranks, g)
+    sharded.local_group_step_fused(ranks, g, n_slices=5)
+    assert torch.all(ranks[0].var == -6.0) and torch.all(ranks[1].var == -6.0)

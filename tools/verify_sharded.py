@@ -24,12 +24,14 @@ def main():
     dev = torch.device("cuda", local)
     torch.cuda.set_device(dev)
     dist.init_process_group("nccl", device_id=dev)
-    elems, workers, steps = 1_000_003, 3, 4
+    elems, workers, steps = 400_003, 3, 3
     ok = True
-    for mode in ("fused", "nccl"):
+    variants = [("fused", "ipc", 1), ("fused", "ipc", 16), ("fused", "symm", 8),
+                ("streams", "ipc", 4), ("nccl", "ipc", 1)]
+    for mode, rdv, chunks in variants:
         for opt, bf16 in ((pkg.OPT_SGD, False), (pkg.OPT_ADAM, True), (pkg.OPT_MOMENTUM, False)):
             sps = ShardedPS(rank, world, local, elems, opt, pkg.HParams(lr=0.01, momentum=0.9),
-                            mode=mode)
+                            mode=mode, rendezvous=rdv, n_chunks=chunks, multicast=False)
             padded = sps.padded
             rng = np.random.default_rng(7)          # same stream on every rank
             var = rng.standard_normal(padded).astype(F)
@@ -47,18 +49,23 @@ def main():
                 partials = [O.numpy_aggregate(gr, False) for gr in allg]
                 O.numpy_apply(opt, var, s0, s1, O.numpy_aggregate(partials, False), ohp)
                 ohp.advance()
-            if mode == "fused":
+            if mode != "nccl":
                 sps.check()
             torch.cuda.synchronize()
             dist.barrier()
             got = sps.var.cpu().numpy()
-            if mode == "fused":
+            if mode != "nccl":
                 good = np.array_equal(got, var)
             else:
                 good = np.allclose(got, var, rtol=1e-5, atol=1e-6)
             ok &= bool(good)
-            print(f"rank {rank}/{world} mode={mode} opt={opt} bf16={bf16} "
-                  f"{'OK' if good else 'MISMATCH ' + str(int((got != var).sum()))}", flush=True)
+            bad = torch.tensor([0 if good else int((got != var).sum()) or 1], device=dev)
+            dist.all_reduce(bad, op=dist.ReduceOp.MAX)      # one line per case, from rank 0
+            if rank == 0:
+                print(f"world={world} mode={mode} rdv={rdv} mc={int(bool(sps.multicast_ptr))} "
+                      f"chunks={chunks} opt={opt} bf16={bf16} "
+                      f"{'OK (all ranks)' if bad.item() == 0 else 'MISMATCH ' + str(bad.item())}",
+                      flush=True)
             del sps
             torch.cuda.empty_cache()
     dist.destroy_process_group()
