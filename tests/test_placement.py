@@ -154,3 +154,43 @@ def test_flat_plan(pkg, n, n_ps, align):
     assert padded >= n and padded % (n_ps * align) == 0 and padded - n < n_ps * align
     assert all(c == padded // n_ps for _, c in shards)
     assert [o for o, _ in shards] == [r * (padded // n_ps) for r in range(n_ps)]
+
+
+# ---- BASELINE configs 3 and 4: the named models' variable lists --------------------------------
+def _model_sizes(name):
+    import json
+    import os
+    path = os.path.join(os.path.dirname(__file__), "golden", "model_shapes.json")
+    shapes = json.load(open(path))[name]
+    sizes = []
+    for _, s in shapes:
+        n = 1
+        for d in s:
+            n *= d
+        sizes.append(n)
+    return sizes
+
+
+@pytest.mark.parametrize("name,tensors,elems,biggest,smallest", [
+    ("resnet50", 161, 25_557_032, 2_359_296, 64),
+    ("bert_large", 391, 335_141_888, 31_254_528, 1_024)])
+def test_model_shape_lists(name, tensors, elems, biggest, smallest):
+    sizes = _model_sizes(name)
+    assert (len(sizes), sum(sizes), max(sizes), min(sizes)) == (tensors, elems, biggest, smallest)
+
+
+@pytest.mark.parametrize("name", ["resnet50", "bert_large"])
+@pytest.mark.parametrize("n_ps", [2, 4, 8])
+def test_round_robin_on_named_models(pkg, name, n_ps):
+    sizes = _model_sizes(name)
+    task, off, fill = pkg.plan_round_robin(sizes, n_ps, 0, 8)
+    assert (task, off, fill) == tuple(PO.round_robin(sizes, n_ps, 0, 8))
+    assert task == [k % n_ps for k in range(len(sizes))]
+    # buckets tile without overlap and hold every variable exactly once
+    for t in range(n_ps):
+        spans = sorted((off[k], off[k] + sizes[k]) for k in range(len(sizes)) if task[k] == t)
+        assert all(a[1] <= b[0] for a, b in zip(spans, spans[1:]))
+        assert spans[-1][1] == fill[t]
+    # round-robin ignores size: the flat plan is the balanced one
+    shards, padded = pkg.plan_flat(sum(sizes), n_ps, 8)
+    assert max(fill) >= padded // n_ps
