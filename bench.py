@@ -282,7 +282,7 @@ def run_sharded(args):
     dist.init_process_group("nccl", device_id=dev)
     sps = ShardedPS(rank, world, local, ELEMS, pkg.OPT_SGD, pkg.HParams(lr=LR), mode=args.mode,
                     n_chunks=args.chunks or None, rendezvous=args.rendezvous,
-                    multicast=args.multicast)
+                    multicast=args.multicast, pull_dtype=args.pull)
     gen = torch.Generator(device=dev)
     gen.manual_seed(42)
     sps.var.copy_(torch.randn(sps.padded, device=dev, generator=gen))
@@ -326,7 +326,8 @@ def run_sharded(args):
             "ms_per_step": round(ms, 4), "higher_is_better": True, "scaling": "weak",
             "vs_baseline": None, "dtype": "f32", "data": "synthetic",
             "config": dict(workload_config(world), mode=sps.mode, chunks=sps.n_chunks,
-                           rendezvous=args.rendezvous, multicast=bool(sps.multicast_ptr)),
+                           rendezvous=args.rendezvous, multicast=bool(sps.multicast_ptr),
+                           pull=args.pull),
             "steps_per_s": round(1e3 / ms, 2),
             "roofline": {"bound": "hbm", "achieved": round(hbm_bytes / (ms * 1e-3) / 1e9, 2),
                          "peak": peak, "unit": "GB/s",
@@ -356,6 +357,8 @@ def main():
     ap.add_argument("--chunks", type=int, default=0,
                     help="pipeline slices of the sharded step (0 = the harness default per world)")
     ap.add_argument("--rendezvous", default="ipc", choices=["ipc", "symm"])
+    ap.add_argument("--pull", default="f32", choices=["f32", "bf16"],
+                    help="dtype of the replicas the pull writes (bf16 halves the pull bytes)")
     ap.add_argument("--multicast", action="store_true",
                     help="pull through an NVSwitch multicast mapping (symm rendezvous only)")
     ap.add_argument("--kernel", default="", help="ldg128 | ldg256 | tma (default: auto)")

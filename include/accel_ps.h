@@ -334,7 +334,12 @@ int accel_dev_free(void *dev_ptr);
  *               once by the owner before the first step;
  *   var_multicast : optional NVSwitch multicast mapping covering every rank's
  *               var replica (one store reaches all replicas, in-switch); NULL
- *               makes the pull `world` unicast peer stores. */
+ *               makes the pull `world` unicast peer stores;
+ *   var_bf16  : optional bf16 [world*shard] replicas, one per rank. When set, the
+ *               pull delivers the updated variables rounded to bf16 (nearest-even)
+ *               into every rank's var_bf16 — half the NVLink bytes — and the fp32
+ *               values stay with the owner only (its shard inside var[rank]).
+ *               For workers that compute in bf16 (SURVEY §8 f, rank 2). */
 #define ACCEL_SHARD_FLAG_WORDS 256
 typedef struct accel_peers {
   int32_t rank;
@@ -344,6 +349,7 @@ typedef struct accel_peers {
   float *const *var;
   uint32_t *const *flags;
   float *var_multicast;
+  uint16_t *const *var_bf16;
 } accel_peers;
 
 /* Push (the worker->PS reduce-scatter, fused): sum this rank's n_workers local

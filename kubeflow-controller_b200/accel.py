@@ -78,7 +78,8 @@ class Peers(ctypes.Structure):
                 ("stage", ctypes.POINTER(ctypes.c_void_p)),
                 ("var", ctypes.POINTER(ctypes.c_void_p)),
                 ("flags", ctypes.POINTER(ctypes.c_void_p)),
-                ("var_multicast", ctypes.c_void_p)]
+                ("var_multicast", ctypes.c_void_p),
+                ("var_bf16", ctypes.POINTER(ctypes.c_void_p))]
 
 
 _lib = None

@@ -144,18 +144,7 @@ __global__ void __launch_bounds__(512) ps_apply_pull(const __grid_constant__ Sha
       for (int e = 0; e < 8; ++e) update<OPT>(v[e], s0[e], s1[e], finish_grad(acc[e], sc), sc);
       if constexpr (SLOTS >= 1) st_state_256(a.slot0 + it * 8, s0);
       if constexpr (SLOTS >= 2) st_state_256(a.slot1 + it * 8, s1);
-      if (a.var_mc != nullptr) {
-        // the pull through the switch: one multicast store lands in every rank's replica
-        st_multimem_128(a.var_mc + var_off + it * 8, v);
-        st_multimem_128(a.var_mc + var_off + it * 8 + 4, v + 4);
-      } else {
-        // the pull as unicast peer stores: own replica first, then the right-hand neighbours
-        for (int k = 0; k < a.world; ++k) {
-          int p = a.rank + k;
-          if (p >= a.world) p -= a.world;
-          st_256(a.var[p] + var_off + it * 8, v);
-        }
-      }
+      pull_item(a, var_off + it * 8, v);
     }
   }
   signal_all(a, kFlagTicketApply, kFlagPull);
@@ -215,6 +204,16 @@ int fill_peers(const accel_peers *peers, uint64_t sub_begin, uint64_t sub_count,
   if (reinterpret_cast<uintptr_t>(peers->var_multicast) & 31)
     return fail(ACCEL_ERR_ALIGN, "var_multicast must be 32-byte aligned");
   a->var_mc = peers->var_multicast;
+  if (peers->var_bf16) {
+    for (int r = 0; r < peers->world; ++r) {
+      if (!peers->var_bf16[r]) return fail(ACCEL_ERR_INVALID, "peer %d has a NULL var_bf16", r);
+      if (reinterpret_cast<uintptr_t>(peers->var_bf16[r]) & 15)
+        return fail(ACCEL_ERR_ALIGN, "peer %d var_bf16 must be 16-byte aligned", r);
+      a->var_bf16[r] = peers->var_bf16[r];
+    }
+    if (peers->var_multicast)
+      return fail(ACCEL_ERR_INVALID, "var_bf16 and var_multicast are mutually exclusive");
+  }
   a->rank = peers->rank;
   a->world = peers->world;
   a->shard = peers->shard_elems;

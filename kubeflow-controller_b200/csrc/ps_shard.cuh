@@ -26,6 +26,7 @@ struct ShardArgs {
   float *slot1;
   const float *sumsq;
   float *var_mc;   // multicast mapping of all ranks' var replicas, or nullptr
+  uint16_t *var_bf16[ACCEL_MAX_PS];  // bf16 replicas (pull target) or all nullptr
   uint64_t shard;  // elements per shard, multiple of 8
   uint64_t sub_begin, sub_count;  // the slice of EVERY shard this launch covers (multiples of 8)
   int rank, world, n_workers;
@@ -99,6 +100,42 @@ __device__ __forceinline__ void st_multimem_128(float *mc, const float *o) {
   asm volatile("multimem.st.weak.global.v4.f32 [%0], {%1,%2,%3,%4};" ::"l"(mc), "f"(o[0]),
                "f"(o[1]), "f"(o[2]), "f"(o[3])
                : "memory");
+}
+// fp32 -> bf16, round to nearest even (finite values; NaN keeps a quiet-NaN pattern)
+__device__ __forceinline__ uint32_t pack_bf16x2(float lo, float hi) {
+  uint32_t r;
+  asm("cvt.rn.bf16x2.f32 %0, %1, %2;" : "=r"(r) : "f"(hi), "f"(lo));
+  return r;
+}
+__device__ __forceinline__ void st_128u(uint16_t *p, const uint32_t (&o)[4]) {
+  asm volatile("st.global.v4.b32 [%0], {%1,%2,%3,%4};" ::"l"(p), "r"(o[0]), "r"(o[1]), "r"(o[2]),
+               "r"(o[3])
+               : "memory");
+}
+// The pull of one item (8 updated values) of rank `a.rank`'s shard.
+__device__ __forceinline__ void pull_item(const ShardArgs &a, uint64_t var_elem, const float (&v)[8]) {
+  if (a.var_bf16[0] != nullptr) {
+    st_state_256(a.var[a.rank] + var_elem, v);      // fp32 master stays with the owner
+    uint32_t h[4];
+#pragma unroll
+    for (int k = 0; k < 4; ++k) h[k] = pack_bf16x2(v[2 * k], v[2 * k + 1]);
+    for (int q = 0; q < a.world; ++q) {
+      int p = a.rank + q;
+      if (p >= a.world) p -= a.world;
+      st_128u(a.var_bf16[p] + var_elem, h);
+    }
+  } else if (a.var_mc != nullptr) {
+    // through the switch: one multicast store lands in every rank's replica
+    st_multimem_128(a.var_mc + var_elem, v);
+    st_multimem_128(a.var_mc + var_elem + 4, v + 4);
+  } else {
+    // unicast peer stores: own replica first, then the right-hand neighbours
+    for (int q = 0; q < a.world; ++q) {
+      int p = a.rank + q;
+      if (p >= a.world) p -= a.world;
+      st_256(a.var[p] + var_elem, v);
+    }
+  }
 }
 __device__ __forceinline__ void ld_256_plain(const float *p, float (&o)[8]) {
   asm volatile("ld.global.L1::no_allocate.v8.f32 {%0,%1,%2,%3,%4,%5,%6,%7}, [%8];"

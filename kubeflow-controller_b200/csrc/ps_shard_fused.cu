@@ -124,11 +124,7 @@ __device__ __forceinline__ void apply_slice(const ShardArgs &a, const Scalars &s
     for (int e = 0; e < 8; ++e) update<OPT>(v[e], s0[e], s1[e], finish_grad(acc[e], sc), sc);
     if constexpr (SLOTS >= 1) st_state_256(a.slot0 + it * 8, s0);
     if constexpr (SLOTS >= 2) st_state_256(a.slot1 + it * 8, s1);
-    for (int q = 0; q < a.world; ++q) {
-      int p = a.rank + q;
-      if (p >= a.world) p -= a.world;
-      st_256(a.var[p] + var_off + it * 8, v);
-    }
+    pull_item(a, var_off + it * 8, v);
   }
 }
 

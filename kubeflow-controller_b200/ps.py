@@ -75,6 +75,56 @@ class ParameterServer:
                                   self.hp, host_var_out, task=self.task, count=self.count)
         self._finish()
 
+    def apply_async(self, worker_grad, stream=None) -> None:
+        """Asynchronous (stale) mode — the example's default (mnist_replica.py:72,
+        sync_replicas=False): one worker's push is applied on its own, no aggregation; TF runs
+        the optimizer's finish step (Adam's beta powers) with every such apply."""
+        self.apply_gradients([worker_grad], stream=stream)
+
+    # ---- checkpoint / restore of this task's shard (TFJobSpec.ModelDir, declared at
+    # vendor/github.com/caicloud/kubeflow-clientset/apis/kubeflow/v1alpha1/types.go:46-47 and
+    # unused by the reference; the example checkpoints to a temp dir, mnist_replica.py:198-215)
+    def save(self, model_dir: str) -> str:
+        import os
+
+        import numpy as np
+        os.makedirs(model_dir, exist_ok=True)
+        path = os.path.join(model_dir, f"ps-{self.task}-of-{self.n_ps}.npz")
+        hp = {name: getattr(self.hp, name) for name, _ in self.hp._fields_}
+        arrays = {"var": self.var.cpu().numpy(), "global_step": np.int64(self.global_step),
+                  "count": np.int64(self.count), "optimizer": np.int64(self.optimizer),
+                  "hp_names": np.array(list(hp)), "hp_values": np.array(list(hp.values()),
+                                                                        dtype=np.float64)}
+        if self.slot0 is not None:
+            arrays["slot0"] = self.slot0.cpu().numpy()
+        if self.slot1 is not None:
+            arrays["slot1"] = self.slot1.cpu().numpy()
+        tmp = path + ".tmp.npz"
+        np.savez(tmp, **arrays)
+        os.replace(tmp, path)       # a reader never sees a half-written checkpoint
+        return path
+
+    def restore(self, model_dir: str) -> None:
+        import os
+
+        import numpy as np
+        path = os.path.join(model_dir, f"ps-{self.task}-of-{self.n_ps}.npz")
+        z = np.load(path)
+        if int(z["count"]) != self.count or int(z["optimizer"]) != self.optimizer:
+            raise ValueError(f"{path} holds a different shard (count {int(z['count'])}, "
+                             f"optimizer {int(z['optimizer'])})")
+        self.var.copy_(torch.from_numpy(z["var"]))
+        if self.slot0 is not None:
+            self.slot0.copy_(torch.from_numpy(z["slot0"]))
+        if self.slot1 is not None:
+            self.slot1.copy_(torch.from_numpy(z["slot1"]))
+        import ctypes
+        fields = dict(self.hp._fields_)
+        for name, value in zip(z["hp_names"], z["hp_values"]):
+            is_float = fields[str(name)] is ctypes.c_float
+            setattr(self.hp, str(name), float(value) if is_float else int(value))
+        self.global_step = int(z["global_step"])
+
     def _finish(self) -> None:
         if self.optimizer == accel.OPT_ADAM:
             accel.adam_advance(self.hp)

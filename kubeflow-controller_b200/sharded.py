@@ -37,7 +37,8 @@ class DevBuffer:
 
     def tensor(self, dtype=torch.float32) -> torch.Tensor:
         item = torch.empty(0, dtype=dtype).element_size()
-        typestr = {torch.float32: "<f4", torch.int32: "<i4", torch.uint8: "|u1"}[dtype]
+        typestr = {torch.float32: "<f4", torch.int32: "<i4", torch.int16: "<i2",
+                   torch.uint8: "|u1"}[dtype]
 
         class _View:
             __cuda_array_interface__ = {"shape": (self.nbytes // item,), "typestr": typestr,
@@ -110,11 +111,16 @@ class ShardedPS:
     def __init__(self, rank: int, world: int, device_index: int, elems: int, optimizer: int,
                  hp: accel.HParams, mode: str = "fused", ctx: accel.Context | None = None,
                  peer_ptrs=None, gpu_ordinals=None, n_chunks: int | None = None,
-                 rendezvous: str = "ipc", multicast: bool = False):
+                 rendezvous: str = "ipc", multicast: bool = False, pull_dtype: str = "f32"):
         if mode not in ("fused", "streams", "nccl"):
             raise ValueError(f"unknown mode {mode!r}")
         if rendezvous not in ("ipc", "symm"):
             raise ValueError(f"unknown rendezvous {rendezvous!r}")
+        if pull_dtype not in ("f32", "bf16"):
+            raise ValueError(f"unknown pull_dtype {pull_dtype!r}")
+        if pull_dtype == "bf16" and (mode == "nccl" or multicast or rendezvous != "ipc"):
+            raise ValueError("the bf16 pull is implemented for the fused paths over ipc rendezvous")
+        self.pull_dtype = pull_dtype
         self.rank, self.world, self.mode = rank, world, mode
         # slices of the step: measured on B200, overlap pays at 2 ranks (4 slices: 0.817 ms vs
         # 0.874 ms) and costs at 8 (1 slice: 1.166 ms, 2: 1.184 ms, 4: 1.299 ms)
@@ -143,6 +149,10 @@ class ShardedPS:
             self.buf_var = DevBuffer(self.padded * 4, device_index)
             self.buf_stage = DevBuffer(self.padded * 4, device_index)
             self.buf_flags = DevBuffer(1024, device_index)
+        # bf16 pull: workers read a bf16 replica, the owner keeps the fp32 master of its shard
+        self.buf_var16 = DevBuffer(self.padded * 2, device_index) if pull_dtype == "bf16" else None
+        self.var_bf16 = self.buf_var16.tensor(torch.int16).view(torch.bfloat16) \
+            if self.buf_var16 else None
         self.var = self.buf_var.tensor()
         self.stage = self.buf_stage.tensor()
         self.flags = self.buf_flags.tensor(torch.int32)
@@ -155,15 +165,18 @@ class ShardedPS:
         n_slices = -(-(self.shard // 8) // (-(-(self.shard // 8) // self.n_chunks)))
         self.launches_per_step = {"fused": 1, "streams": 2 * n_slices + 1, "nccl": 2}[mode]
         if peer_ptrs is None:
-            mine = (self.buf_var.export(), self.buf_stage.export(), self.buf_flags.export())
+            mine = (self.buf_var.export(), self.buf_stage.export(), self.buf_flags.export(),
+                    self.buf_var16.export() if self.buf_var16 else None)
             handles = exchange(mine, world)
             peer_ptrs = []
             with torch.cuda.device(device_index):
-                for r, (hv, hs, hf) in enumerate(handles):
+                for r, (hv, hs, hf, h16) in enumerate(handles):
                     if r == rank:
-                        peer_ptrs.append((self.buf_var.ptr, self.buf_stage.ptr, self.buf_flags.ptr))
+                        peer_ptrs.append((self.buf_var.ptr, self.buf_stage.ptr, self.buf_flags.ptr,
+                                          self.buf_var16.ptr if self.buf_var16 else 0))
                     else:
-                        peer_ptrs.append((open_peer(hv), open_peer(hs), open_peer(hf)))
+                        peer_ptrs.append((open_peer(hv), open_peer(hs), open_peer(hf),
+                                          open_peer(h16) if h16 else 0))
         self.set_peers(peer_ptrs)
 
     def set_peers(self, peer_ptrs):
@@ -172,14 +185,17 @@ class ShardedPS:
         self._var_arr = (ctypes.c_void_p * w)(*[p[0] for p in peer_ptrs])
         self._stage_arr = (ctypes.c_void_p * w)(*[p[1] for p in peer_ptrs])
         self._flags_arr = (ctypes.c_void_p * w)(*[p[2] for p in peer_ptrs])
+        self._var16_arr = None
+        if self.pull_dtype == "bf16":
+            self._var16_arr = (ctypes.c_void_p * w)(*[p[3] for p in peer_ptrs])
         self.peers = accel.Peers(self.rank, w, self.shard, self._stage_arr, self._var_arr,
-                                 self._flags_arr, self.multicast_ptr or None)
+                                 self._flags_arr, self.multicast_ptr or None, self._var16_arr)
         # world = 1 view onto the same stage buffer: the local pre-sum of nccl mode
         self._solo_var = (ctypes.c_void_p * 1)(self.buf_var.ptr)
         self._solo_stage = (ctypes.c_void_p * 1)(self.buf_stage.ptr)
         self._solo_flags = (ctypes.c_void_p * 1)(self.buf_flags.ptr)
         self.solo = accel.Peers(0, 1, self.padded, self._solo_stage, self._solo_var,
-                                self._solo_flags, None)
+                                self._solo_flags, None, None)
 
     @property
     def var_shard(self) -> torch.Tensor:
@@ -245,7 +261,7 @@ class ShardedPS:
 
 
 def local_group(world: int, elems: int, optimizer: int, hp_factory, device_index: int = 0,
-                n_chunks: int = 1):
+                n_chunks: int = 1, pull_dtype: str = "f32"):
     """`world` ranks emulated on ONE GPU inside one process (tests): every rank's buffers are
     plain local allocations and the phases are run rank after rank on one stream, so every
     device-side wait is already satisfied when its kernel starts."""
@@ -253,8 +269,10 @@ def local_group(world: int, elems: int, optimizer: int, hp_factory, device_index
     ranks = []
     for r in range(world):
         ranks.append(ShardedPS(r, world, device_index, elems, optimizer, hp_factory(), ctx=ctx,
-                               peer_ptrs=[(0, 0, 0)] * world, n_chunks=n_chunks))
-    ptrs = [(x.buf_var.ptr, x.buf_stage.ptr, x.buf_flags.ptr) for x in ranks]
+                               peer_ptrs=[(0, 0, 0, 0)] * world, n_chunks=n_chunks,
+                               pull_dtype=pull_dtype))
+    ptrs = [(x.buf_var.ptr, x.buf_stage.ptr, x.buf_flags.ptr,
+             x.buf_var16.ptr if x.buf_var16 else 0) for x in ranks]
     for x in ranks:
         x.set_peers(ptrs)
     return ranks

@@ -316,3 +316,49 @@ def test_config2_full_size(pkg, ctx):
     O.COracle().ps_step(O.SGD, h_var, None, None, h_g, O.HParams(lr=lr))
     got = var.cpu().numpy()
     assert np.array_equal(got, h_var), f"{(got != h_var).sum()} of {n} elements differ"
+
+
+# ---- asynchronous applies, checkpoint / restore -------------------------------
+def test_async_mode_applies_each_push_alone(pkg):
+    """The example's default (sync_replicas=False): each worker push is applied by itself, in
+    arrival order, Adam's beta powers advancing with every apply."""
+    sizes = [784 * 100, 100, 100 * 10, 10]
+    ps = pkg.ParameterServer(task_index=0, n_ps=1, var_elems=sizes, optimizer=pkg.OPT_ADAM,
+                             hparams=pkg.HParams(lr=0.01), align_elems=4)
+    rng = np.random.default_rng(0)
+    var = (0.05 * rng.standard_normal(ps.count)).astype(F)
+    ps.var.copy_(torch.from_numpy(var))
+    m, v = np.zeros(ps.count, F), np.zeros(ps.count, F)
+    ohp = O.HParams(lr=0.01)
+    for push in range(12):                      # 4 workers x 3 local steps, interleaved
+        g = (0.01 * rng.standard_normal(ps.count)).astype(F)
+        ps.apply_async(torch.from_numpy(g).to(DEV))
+        O.numpy_ps_step(O.ADAM, var, m, v, [g], ohp)
+        ohp.advance()
+    assert ps.global_step == 12
+    assert np.array_equal(ps.pull().cpu().numpy(), var)
+
+
+def test_checkpoint_restore_resumes_bit_exact(pkg, tmp_path):
+    sizes = [1000, 24, 4096]
+
+    def make():
+        return pkg.ParameterServer(task_index=0, n_ps=1, var_elems=sizes, optimizer=pkg.OPT_ADAM,
+                                   hparams=pkg.HParams(lr=0.01), align_elems=8)
+    rng = np.random.default_rng(1)
+    a = make()
+    a.var.copy_(torch.from_numpy(rng.standard_normal(a.count).astype(F)))
+    grads = [[torch.from_numpy((0.01 * rng.standard_normal(a.count)).astype(F)).to(DEV)
+              for _ in range(2)] for _ in range(6)]
+    for g in grads[:3]:
+        a.apply_gradients(g)
+    a.save(str(tmp_path))
+    for g in grads[3:]:
+        a.apply_gradients(g)
+    b = make()                                   # a fresh replica resumes from the checkpoint
+    b.restore(str(tmp_path))
+    assert b.global_step == 3 and b.hp.beta1_power == pytest.approx(0.9 ** 4, rel=1e-6)
+    for g in grads[3:]:
+        b.apply_gradients(g)
+    assert torch.equal(a.var, b.var) and torch.equal(a.slot0, b.slot0) and torch.equal(a.slot1, b.slot1)
+    assert a.hp.beta2_power == b.hp.beta2_power and b.global_step == 6

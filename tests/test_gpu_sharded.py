@@ -112,7 +112,7 @@ def test_shard_argument_errors(pkg):
         x.wait_pull()
     with pytest.raises(pkg.AccelError, match="aligned"):
         x.push([torch.ones(x.padded + 1, device=DEV)[1:]])
-    bad = pkg.accel.Peers(0, 2, 12, x._stage_arr, x._var_arr, x._flags_arr, None)
+    bad = pkg.accel.Peers(0, 2, 12, x._stage_arr, x._var_arr, x._flags_arr, None, None)
     with pytest.raises(pkg.AccelError, match="multiple of 8"):
         x.push([torch.ones(x.padded, device=DEV)], peers=bad)
     with pytest.raises(pkg.AccelError, match="sub-range"):
@@ -188,3 +188,36 @@ def test_one_kernel_step_then_three_phase_step_share_epochs(pkg):
     sharded.local_group_step(ranks, g)
     sharded.local_group_step_fused(ranks, g, n_slices=5)
     assert torch.all(ranks[0].var == -6.0) and torch.all(ranks[1].var == -6.0)
+
+
+@pytest.mark.parametrize("world,one_kernel", [(2, False), (4, True), (8, True)])
+@pytest.mark.parametrize("opt", [O.SGD, O.ADAM])
+def test_bf16_pull(pkg, world, one_kernel, opt):
+    """Pull in bf16 (SURVEY 8 f, rank 2): every rank's bf16 replica holds the updated variables
+    rounded to nearest-even; the fp32 master exists only in the owner's shard."""
+    from kubeflow_controller_b200 import sharded
+    ranks = sharded.local_group(world, 200_003, opt, lambda: pkg.HParams(lr=0.01),
+                                n_chunks=2, pull_dtype="bf16")
+    padded, shard = ranks[0].padded, ranks[0].shard
+    rng = np.random.default_rng(world)
+    var = rng.standard_normal(padded).astype(F)
+    s0, s1 = np.zeros(padded, F), np.zeros(padded, F)
+    for x in ranks:
+        x.var.copy_(_dev(var))
+    ohp = O.HParams(lr=0.01)
+    for step in range(2):
+        gpr = [[(0.01 * rng.standard_normal(padded)).astype(F) for _ in range(2)]
+               for _ in range(world)]
+        dg = [[_dev(g) for g in gr] for gr in gpr]
+        if one_kernel:
+            sharded.local_group_step_fused(ranks, dg, n_slices=3)
+        else:
+            sharded.local_group_step(ranks, dg)
+        O.numpy_apply(opt, var, s0, s1, _oracle_hier(gpr, False), ohp)
+        ohp.advance()
+    want16 = O.f32_to_bf16_bits(var)
+    for x in ranks:
+        got16 = x.var_bf16.view(torch.int16).cpu().numpy().view(np.uint16)
+        assert np.array_equal(got16, want16), f"rank {x.rank} bf16 replica differs"
+        lo, hi = x.rank * shard, (x.rank + 1) * shard
+        assert np.array_equal(x.var[lo:hi].cpu().numpy(), var[lo:hi])   # fp32 master, own shard
