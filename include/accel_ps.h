@@ -249,7 +249,11 @@ int accel_host_unregister(void *host_ptr);
 
 /* ---- placement: the contract pkg/tensorflow emits ------------------------ */
 
-typedef enum accel_replica_type { ACCEL_REPLICA_PS = 0, ACCEL_REPLICA_WORKER = 1 } accel_replica_type;
+typedef enum accel_replica_type {
+  ACCEL_REPLICA_PS = 0,
+  ACCEL_REPLICA_WORKER = 1,
+  ACCEL_REPLICA_LOCAL = 2 /* only meaningful to accel_tfjob_is_local_job */
+} accel_replica_type;
 
 /* Action types in the order of pkg/tensorflow/types.go:28-34. */
 typedef enum accel_action {
@@ -273,6 +277,11 @@ typedef struct accel_event {
 int accel_tfjob_action(int worker_replicas, int ps_replicas, int succeeded_workers,
                        int worker_services, int ps_services, int active_workers, int active_ps,
                        accel_event *out, int *n_out, int *composed);
+
+/* checker.IsLocalJob (pkg/checker/checker.go:8-14): a job is local iff its FIRST
+ * replica spec has type Local. replica_types[n] are accel_replica_type values in
+ * spec order. Returns 1 / 0, or a negative status. */
+int accel_tfjob_is_local_job(const int *replica_types, int n);
 
 /* "<job>-<type lower-cased>-<index>" — DistributedJob.getServiceName
  * (pkg/tensorflow/distributed.go:161-163). Returns the length written
@@ -377,6 +386,15 @@ int accel_shard_apply_pull(accel_ctx *ctx, const accel_peers *peers, int optimiz
                            float *slot1, int n_contrib, const accel_hparams *hp,
                            const float *grad_sumsq_dev, uint64_t sub_begin, uint64_t sub_count,
                            uint32_t epoch, accel_stream_t stream);
+
+/* Block the stream until every rank's push of `epoch` (0 = latest) has landed in
+ * this rank's stage slots (device-side, bounded). Needed only when something
+ * has to read the slots between push and apply_pull — global-norm clipping:
+ * accel_grad_sumsq over the `world` slots of the own shard (they are `world`
+ * fp32 "worker" gradients of shard_elems each), an all-reduce of that scalar
+ * across ranks, then accel_shard_apply_pull with the result (e). */
+int accel_shard_wait_push(accel_ctx *ctx, const accel_peers *peers, uint32_t epoch,
+                          accel_stream_t stream);
 
 /* Block the stream until every rank's apply_pull of `epoch` (0 = latest) has
  * landed in this rank's var replica (device-side, bounded wait). */

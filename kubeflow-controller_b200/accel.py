@@ -18,7 +18,7 @@ F32, BF16 = 0, 1
 AGG_SUM, AGG_MEAN = 0, 1
 OPT_SGD, OPT_MOMENTUM, OPT_ADAM = 0, 1, 2
 KERNEL_AUTO, KERNEL_LDG128, KERNEL_LDG256, KERNEL_TMA = 0, 1, 2, 3
-REPLICA_PS, REPLICA_WORKER = 0, 1
+REPLICA_PS, REPLICA_WORKER, REPLICA_LOCAL = 0, 1, 2
 MAX_WORKERS, MAX_PS = 64, 16
 ACTION_NAMES = ["ShouldAddPS", "ShouldAddPSService", "ShouldAddWorker",
                 "ShouldAddWorkerService", "ShouldDelete", "Nothing"]
@@ -29,10 +29,10 @@ SYMBOLS = [
     "accel_ctx_gpu_of", "accel_ctx_set_kernel", "accel_plan_flat", "accel_plan_round_robin",
     "accel_apply_sgd", "accel_apply_momentum", "accel_apply_adam", "accel_adam_advance",
     "accel_grad_sumsq", "accel_grad_sumsq_static", "accel_ps_step_host", "accel_host_register", "accel_host_unregister",
-    "accel_tfjob_action", "accel_tfjob_service_key", "accel_tfjob_cluster_spec",
+    "accel_tfjob_action", "accel_tfjob_is_local_job", "accel_tfjob_service_key", "accel_tfjob_cluster_spec",
     "accel_tfjob_labels", "accel_tfjob_parse_argv", "accel_ipc_export", "accel_ipc_open",
     "accel_ipc_close", "accel_dev_alloc", "accel_dev_free", "accel_shard_push",
-    "accel_shard_apply_pull", "accel_shard_wait_pull", "accel_shard_step", "accel_shard_step_fused",
+    "accel_shard_apply_pull", "accel_shard_wait_push", "accel_shard_wait_pull", "accel_shard_step", "accel_shard_step_fused",
     "accel_shard_step_local_group", "accel_shard_check",
 ]
 
@@ -137,6 +137,8 @@ def load_library() -> ctypes.CDLL:
     L.accel_shard_apply_pull.argtypes = [vp, ctypes.POINTER(Peers), i32, vp, vp, i32, php, vp,
                                          u64, u64, u32, vp]
     L.accel_shard_wait_pull.argtypes = [vp, ctypes.POINTER(Peers), u32, vp]
+    L.accel_shard_wait_push.argtypes = [vp, ctypes.POINTER(Peers), u32, vp]
+    L.accel_tfjob_is_local_job.argtypes = [ctypes.POINTER(i32), i32]
     L.accel_shard_step.argtypes = [vp, ctypes.POINTER(Peers), i32, vp, vp, pvp, i32, i32, i32, php,
                                    vp, i32, vp]
     L.accel_shard_step_fused.argtypes = L.accel_shard_step.argtypes

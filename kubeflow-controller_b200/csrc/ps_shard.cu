@@ -154,6 +154,10 @@ __global__ void ps_wait_pull(const __grid_constant__ ShardArgs a) {
   wait_all(a.flags[a.rank], kFlagPull, a.world, a.epoch);
 }
 
+__global__ void ps_wait_push(const __grid_constant__ ShardArgs a) {
+  wait_all(a.flags[a.rank], kFlagPush, a.world, a.epoch);
+}
+
 template <typename G>
 static int launch_push(const ShardArgs &a, int grid, cudaStream_t s) {
   const int threads = 256;
@@ -378,6 +382,22 @@ int accel_shard_apply_pull(accel_ctx *ctx, const accel_peers *peers, int optimiz
 int accel_shard_wait_pull(accel_ctx *ctx, const accel_peers *peers, uint32_t epoch,
                           accel_stream_t stream) {
   return do_wait_pull(ctx, peers, epoch, static_cast<cudaStream_t>(stream));
+}
+
+int accel_shard_wait_push(accel_ctx *ctx, const accel_peers *peers, uint32_t epoch,
+                          accel_stream_t stream) {
+  ShardArgs a;
+  int rc = fill_peers(peers, 0, 0, &a);
+  if (rc) return rc;
+  TaskState *ts = nullptr;
+  rc = task_state(ctx, peers->rank, &ts);
+  if (rc) return rc;
+  if (ts->shard_epoch == 0)
+    return fail(ACCEL_ERR_STATE, "accel_shard_wait_push before any accel_shard_push");
+  a.epoch = epoch ? epoch : ts->shard_epoch;
+  ps_wait_push<<<1, 32, 0, static_cast<cudaStream_t>(stream)>>>(a);
+  ACCEL_CUDA(cudaGetLastError());
+  return ACCEL_OK;
 }
 
 int accel_shard_step(accel_ctx *ctx, const accel_peers *peers, int optimizer, float *slot0,

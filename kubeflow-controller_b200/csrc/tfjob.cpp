@@ -300,6 +300,21 @@ int accel_tfjob_action(int worker_replicas, int ps_replicas, int succeeded_worke
   return ACCEL_OK;
 }
 
+int accel_tfjob_is_local_job(const int *replica_types, int n) {
+  if (!replica_types || n < 1) return fail(ACCEL_ERR_INVALID, "a TFJob needs at least one spec");
+  tfjob::TFJob job;
+  for (int i = 0; i < n; ++i) {
+    tfjob::ReplicaType t;
+    if (replica_types[i] == ACCEL_REPLICA_LOCAL) {
+      t = tfjob::ReplicaType::Local;
+    } else if (!to_type(replica_types[i], &t)) {
+      return fail(ACCEL_ERR_INVALID, "unknown replica_type %d", replica_types[i]);
+    }
+    job.specs.push_back({1, t, {}, {}});
+  }
+  return tfjob::IsLocalJob(job) ? 1 : 0;
+}
+
 int accel_tfjob_service_key(const char *job_name, int replica_type, int index, char *buf,
                             size_t buflen) {
   tfjob::ReplicaType t;

@@ -26,6 +26,14 @@ def action(workers, ps, succeeded=0, worker_services=0, ps_services=0, active_wo
         bool(composed.value)
 
 
+def is_local_job(replica_types) -> bool:
+    """checker.IsLocalJob (pkg/checker/checker.go:8-14): Specs[0].TFReplicaType == Local."""
+    L = accel.load_library()
+    codes = {"PS": accel.REPLICA_PS, "Worker": accel.REPLICA_WORKER, "Local": accel.REPLICA_LOCAL}
+    arr = (ctypes.c_int * len(replica_types))(*[codes[t] for t in replica_types])
+    return bool(accel.check(L.accel_tfjob_is_local_job(arr, len(replica_types))))
+
+
 def service_key(job: str, typ: str, index: int) -> str:
     """getServiceName (distributed.go:161-163)."""
     L = accel.load_library()

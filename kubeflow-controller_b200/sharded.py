@@ -218,6 +218,18 @@ class ShardedPS:
             accel._ptr(self.slot1), n_contrib, ctypes.byref(self.hp), accel._ptr(sumsq),
             sub[0], sub[1], epoch, accel._stream_handle(stream)))
 
+    def wait_push(self, stream=None, epoch=0):
+        accel.check(self.lib.accel_shard_wait_push(self.ctx.handle, ctypes.byref(self.peers),
+                                                   epoch, accel._stream_handle(stream)))
+
+    def shard_sumsq(self, out, stream=None):
+        """Sum of squares of THIS shard's aggregated gradient (the `world` stage slots summed in
+        rank order) into out[0]; call after wait_push. Add the ranks' results for the global
+        norm."""
+        slots = [self.stage[s * self.shard:(s + 1) * self.shard] for s in range(self.world)]
+        self.ctx.grad_sumsq(slots, out, aggregate=accel.AGG_SUM, task=self.rank,
+                            count=self.shard, stream=stream)
+
     def wait_pull(self, stream=None, epoch=0):
         accel.check(self.lib.accel_shard_wait_pull(self.ctx.handle, ctypes.byref(self.peers),
                                                    epoch, accel._stream_handle(stream)))
@@ -240,7 +252,21 @@ class ShardedPS:
     def step(self, grads, stream=None, sumsq=None):
         """grads: this rank's local worker gradients, each `padded` elements."""
         n_contrib = len(grads) * self.world
-        if self.mode in ("fused", "streams"):
+        if self.hp.clip_norm > 0 and sumsq is None and self.mode != "nccl":
+            # global-norm clipping needs the whole aggregated gradient's norm before any shard
+            # is applied: push, reduce the per-shard sums of squares across ranks, then apply
+            import torch.distributed as dist
+            if self.hp.aggregate != accel.AGG_SUM:
+                raise ValueError("clipping in the sharded step is implemented for SUM aggregation")
+            ss = torch.zeros(1, device=self.device)
+            epoch = self.push(grads, stream)
+            self.wait_push(stream, epoch)
+            self.shard_sumsq(ss, stream)
+            if self.world > 1:
+                dist.all_reduce(ss, op=dist.ReduceOp.SUM)
+            self.apply_pull(n_contrib, ss, stream, epoch=epoch)
+            self.wait_pull(stream, epoch)
+        elif self.mode in ("fused", "streams"):
             fn = self.lib.accel_shard_step_fused if self.mode == "fused" \
                 else self.lib.accel_shard_step
             accel.check(fn(

@@ -84,3 +84,41 @@ def test_argument_errors_without_touching_a_device(pkg):
     buf = ctypes.create_string_buffer(4)
     assert L.accel_tfjob_service_key(b"a-long-job-name", 0, 0, buf, 4) == -5   # BUFSIZE
     assert b"bytes" in L.accel_last_error()
+
+
+def test_go_wrapper_binds_only_declared_symbols():
+    """The cgo wrapper cannot be compiled here (no Go toolchain); at least every C symbol, type
+    and constant it names must exist in include/accel_ps.h."""
+    header = open(os.path.join(ROOT, "include", "accel_ps.h")).read()
+    go_dir = os.path.join(ROOT, "kubeflow-controller_b200", "go", "pkg", "accel")
+    used = set()
+    for f in os.listdir(go_dir):
+        if f.endswith(".go"):
+            used |= set(re.findall(r"\bC\.((?:accel|ACCEL)_[A-Za-z0-9_]+)", open(os.path.join(go_dir, f)).read()))
+    assert used, "no C references found in the Go wrapper"
+    missing = sorted(u for u in used if not re.search(r"\b" + re.escape(u) + r"\b", header))
+    assert not missing, f"Go wrapper references undeclared C names: {missing}"
+    # and call arity: every C.accel_xxx(...) call passes as many arguments as the prototype has
+    protos = {}
+    flat = re.sub(r"/\*.*?\*/", "", header, flags=re.S)
+    for m in re.finditer(r"\b(accel_[a-z0-9_]+)\s*\(([^;{]*?)\)\s*;", flat, flags=re.S):
+        args = m.group(2).strip()
+        protos[m.group(1)] = 0 if args in ("", "void") else args.count(",") + 1
+    for f in os.listdir(go_dir):
+        if not f.endswith(".go"):
+            continue
+        src = open(os.path.join(go_dir, f)).read()
+        for m in re.finditer(r"C\.(accel_[a-z0-9_]+)\(", src):
+            if m.group(1) not in protos:      # a type conversion such as C.accel_stream_t(...)
+                continue
+            depth, i, commas = 1, m.end(), 0
+            while depth:
+                c = src[i]
+                depth += c in "([{"
+                depth -= c in ")]}"
+                commas += (c == "," and depth == 1)
+                i += 1
+            inner = src[m.end():i - 1].strip()
+            n_args = 0 if not inner else commas + 1
+            assert n_args == protos[m.group(1)], (
+                f"{f}: C.{m.group(1)} called with {n_args} args, header declares {protos[m.group(1)]}")

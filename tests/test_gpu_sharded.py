@@ -221,3 +221,38 @@ def test_bf16_pull(pkg, world, one_kernel, opt):
         assert np.array_equal(got16, want16), f"rank {x.rank} bf16 replica differs"
         lo, hi = x.rank * shard, (x.rank + 1) * shard
         assert np.array_equal(x.var[lo:hi].cpu().numpy(), var[lo:hi])   # fp32 master, own shard
+
+
+def test_sharded_global_norm_clip(pkg):
+    """clip_by_global_norm across shards: per-shard sums of squares of the aggregated gradient
+    (wait_push + accel_grad_sumsq over the stage slots), added across ranks, then apply_pull."""
+    from kubeflow_controller_b200 import sharded
+    world, workers = 4, 2
+    ranks = sharded.local_group(world, 120_000, pkg.OPT_MOMENTUM,
+                                lambda: pkg.HParams(lr=0.1, momentum=0.9, clip_norm=0.05))
+    padded = ranks[0].padded
+    rng = np.random.default_rng(4)
+    var = rng.standard_normal(padded).astype(F)
+    for x in ranks:
+        x.var.copy_(_dev(var))
+    gpr = [[(0.01 * rng.standard_normal(padded)).astype(F) for _ in range(workers)]
+           for _ in range(world)]
+    epochs = [x.push([_dev(g) for g in gr]) for x, gr in zip(ranks, gpr)]
+    parts = torch.zeros(world, device=DEV)
+    for x in ranks:
+        x.wait_push(epoch=epochs[0])
+        x.shard_sumsq(parts[x.rank:x.rank + 1])
+    total = parts.sum().reshape(1)                    # the all-reduce of a real group
+    for x in ranks:
+        x.apply_pull(world * workers, total, epoch=epochs[0])
+    for x in ranks:
+        x.wait_pull(epoch=epochs[0])
+        x.check()
+    g = _oracle_hier(gpr, False)
+    ref_ss = float(O.numpy_sumsq(g))
+    assert abs(total.item() - ref_ss) <= 1e-5 * ref_ss
+    acc = np.zeros(padded, F)
+    O.numpy_apply(O.MOMENTUM, var, acc, None, g * O.numpy_clip_scale(F(total.item()), 0.05),
+                  O.HParams(lr=0.1, momentum=0.9))
+    for x in ranks:     # with the SAME sum of squares the rest is bit-exact
+        assert np.array_equal(x.var.cpu().numpy(), var)

@@ -194,3 +194,11 @@ def test_round_robin_on_named_models(pkg, name, n_ps):
     # round-robin ignores size: the flat plan is the balanced one
     shards, padded = pkg.plan_flat(sum(sizes), n_ps, 8)
     assert max(fill) >= padded // n_ps
+
+
+@pytest.mark.parametrize("first,second,want", [
+    # the reference's own table, pkg/checker/checker_test.go:10-38
+    ("Local", None, True), ("PS", "Local", False), ("PS", "Worker", False), ("Local", "PS", True)])
+def test_is_local_job_table(P, first, second, want):
+    specs = [first] + ([second] if second else [])
+    assert P.is_local_job(specs) is want

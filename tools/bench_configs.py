@@ -90,6 +90,27 @@ def main():
     if not args.quick:
         for w in (1, 2, 3, 4, 16):
             cases.append((f"workers={w} 100M", 0, False, w, 100_000_000))
+    # config 1 (plumbing): the example's model (79,510 fp32), 1 PS + 2 workers, through the
+    # host-buffer call, wall clock per step including copies and synchronisation
+    import time
+    for opt in (0, 2):
+        n, workers = 79_510, 2
+        var = torch.randn(n, device="cuda:0")
+        s0 = torch.zeros(n, device="cuda:0") if opt else None
+        s1 = torch.zeros(n, device="cuda:0") if opt == 2 else None
+        hg = [(torch.randn(n) * 0.01).pin_memory() for _ in range(workers)]
+        hout = torch.empty(n).pin_memory()
+        hp = pkg.HParams(lr=0.5 if opt == 0 else 0.01)
+        for _ in range(20):
+            ctx.ps_step_host(opt, var, s0, s1, hg, hp, hout)
+        t0 = time.perf_counter()
+        for _ in range(200):      # the example's train_steps (mnist_replica.py:68)
+            ctx.ps_step_host(opt, var, s0, s1, hg, hp, hout)
+        dt = (time.perf_counter() - t0) / 200
+        print(json.dumps({"case": "cfg1 mnist 1PS+2W host step", "opt": names[opt], "grad": "f32",
+                          "workers": workers, "elems": n, "us_per_step": round(dt * 1e6, 1),
+                          "steps_per_s": round(1 / dt, 1),
+                          "reference_doc_log_global_steps_per_s": 356}), flush=True)
     for label, opt, bf16, workers, n in cases:
         r = run(ctx, opt, bf16, workers, n, 7 if n > (1 << 26) else 15, flush)
         r.update({"case": label, "opt": names[opt], "grad": "bf16" if bf16 else "f32",
