@@ -20,16 +20,18 @@
 namespace accel {
 
 // ---- push: local N-way sum fused with the reduce-scatter -----------------------
-// Items of 8 elements. Logical item j maps to arena element
-// ((rank+1)*shard + 8j) mod (world*shard): every rank starts with its right-hand
-// neighbour's shard, so at any moment the `world` ranks store to `world` different
-// destinations and no GPU's NVLink ingress is the hot spot.
+// Items of 8 elements, handed out in granules of kPushGranule items. Granule g of a rank goes
+// to destination (rank + 1 + g) mod world: consecutive granules go to consecutive owners, so
+// through the whole kernel every rank is storing to ALL owners at once (its own included) —
+// NVLink egress and ingress are busy from the first tile to the last, and no owner is a hot
+// spot at any moment.
 template <typename G, int NW, int U>
 __global__ void __launch_bounds__(512) ps_push(const __grid_constant__ ShardArgs a) {
   const uint64_t shard_items = a.shard / 8;
   const uint64_t sub_items = a.sub_count / 8;   // items per shard in this launch
   const uint64_t sub_first = a.sub_begin / 8;
-  const uint64_t n_items = sub_items * a.world;
+  const uint64_t granules = (sub_items + kPushGranule - 1) / kPushGranule;   // per owner
+  const uint64_t n_items = granules * kPushGranule * a.world;
   const uint64_t tile = static_cast<uint64_t>(blockDim.x) * U;
   const int n = NW > 0 ? NW : a.n_workers;
 
@@ -43,12 +45,13 @@ __global__ void __launch_bounds__(512) ps_push(const __grid_constant__ ShardArgs
 #pragma unroll
     for (int j = 0; j < U; ++j) {
       const uint64_t l = base + static_cast<uint64_t>(j) * blockDim.x + threadIdx.x;
-      ok[j] = l < n_items;
-      const uint64_t k = l / sub_items;          // k-th destination of this rank's rotation
-      int c = a.rank + 1 + static_cast<int>(k);
+      const uint64_t g = l / kPushGranule;
+      const uint64_t in_shard = (g / a.world) * kPushGranule + (l % kPushGranule);
+      ok[j] = l < n_items && in_shard < sub_items;
+      int c = a.rank + 1 + static_cast<int>(g % a.world);
       if (c >= a.world) c -= a.world;
       owner[j] = ok[j] ? c : a.rank;
-      const uint64_t within = sub_first + (l - k * sub_items);
+      const uint64_t within = sub_first + (ok[j] ? in_shard : 0);
       item[j] = static_cast<uint64_t>(owner[j]) * shard_items + within;
       dst[j] = static_cast<uint64_t>(a.rank) * shard_items + within;
     }

@@ -15,6 +15,7 @@ constexpr int kFlagTicketPush = 32;
 constexpr int kFlagTicketApply = 33;
 constexpr int kFlagSliceTicket = 64;  // [64,128): per-slice tickets of the one-kernel step
 constexpr int kFlagStatus = 48;  // 0 ok, else error code | (waited-for rank << 8)
+constexpr int kPushGranule = 256;  // items (8 elements each) sent to one owner before the next
 constexpr unsigned long long kSpinTimeoutNs = 2000000000ull;  // 2 s
 
 struct ShardArgs {

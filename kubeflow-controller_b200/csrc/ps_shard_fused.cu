@@ -55,14 +55,18 @@ template <typename G, int NW>
 __device__ __forceinline__ void push_slice(const ShardArgs &a, uint64_t sub_first,
                                            uint64_t sub_items, int bid, int nb) {
   const uint64_t shard_items = a.shard / 8;
-  const uint64_t n_items = sub_items * a.world;
+  const uint64_t granules = (sub_items + kPushGranule - 1) / kPushGranule;   // per owner
+  const uint64_t n_items = granules * kPushGranule * a.world;
   const int n = NW > 0 ? NW : a.n_workers;
   for (uint64_t l = static_cast<uint64_t>(bid) * blockDim.x + threadIdx.x; l < n_items;
        l += static_cast<uint64_t>(nb) * blockDim.x) {
-    const uint64_t k = l / sub_items;
-    int c = a.rank + 1 + static_cast<int>(k);  // rotation: start with the right-hand neighbour
+    // granule g goes to owner (rank + 1 + g) mod world: all owners are written all the time
+    const uint64_t g_idx = l / kPushGranule;
+    const uint64_t in_shard = (g_idx / a.world) * kPushGranule + (l % kPushGranule);
+    if (in_shard >= sub_items) continue;
+    int c = a.rank + 1 + static_cast<int>(g_idx % a.world);
     if (c >= a.world) c -= a.world;
-    const uint64_t within = sub_first + (l - k * sub_items);
+    const uint64_t within = sub_first + in_shard;
     const uint64_t item = static_cast<uint64_t>(c) * shard_items + within;
     float acc[8];
     if constexpr (NW > 0) {
