@@ -290,11 +290,13 @@ static int grid_for(const TaskState &ts, uint64_t items, int ctas_per_sm) {
   return grid < 1 ? 1 : grid;
 }
 
-// ctas_per_sm: 2 fills the register file (2 x 256 threads x 96 registers); the pipelined step
-// passes 1 so that the apply_pull CTAs of the previous slice can be resident beside the push.
+// ctas_per_sm: grid size in CTAs per SM. 4 measured best for the NVLink-bound cases (peer-store
+// rate 650 GB/s at 2, 669 at 4, flat beyond); with 8 gradients only 2 are resident (96 registers)
+// and the rest queue. The two-stream pipelined step passes 1 so that the apply_pull CTAs of the
+// previous slice can be resident beside the push.
 static int do_push(accel_ctx *ctx, const accel_peers *peers, const void *const *grads,
                    int n_workers, int grad_dtype, uint64_t sub_begin, uint64_t sub_count,
-                   cudaStream_t s, uint32_t *epoch_out, int ctas_per_sm = 2) {
+                   cudaStream_t s, uint32_t *epoch_out, int ctas_per_sm = 4) {
   ShardArgs a;
   int rc = fill_peers(peers, sub_begin, sub_count, &a);
   if (rc) return rc;
@@ -305,6 +307,7 @@ static int do_push(accel_ctx *ctx, const accel_peers *peers, const void *const *
   if (rc) return rc;
   a.epoch = ++ts->shard_epoch;  // every push opens a new epoch
   if (epoch_out) *epoch_out = a.epoch;
+  if (ctx->tuning.ctas_per_sm) ctas_per_sm = ctx->tuning.ctas_per_sm;   // sweep knob
   const int grid = grid_for(*ts, a.sub_count / 8 * a.world, ctas_per_sm);
   return grad_dtype == ACCEL_BF16 ? launch_push<bf16_t>(a, grid, s) : launch_push<float>(a, grid, s);
 }
@@ -324,6 +327,7 @@ static int do_apply_pull(accel_ctx *ctx, const accel_peers *peers, int optimizer
   if (ts->shard_epoch == 0)
     return fail(ACCEL_ERR_STATE, "accel_shard_apply_pull before any accel_shard_push");
   a.epoch = epoch ? epoch : ts->shard_epoch;
+  if (ctx->tuning.ctas_per_sm) ctas_per_sm = ctx->tuning.ctas_per_sm;   // sweep knob
   const int grid = grid_for(*ts, a.sub_count / 8, ctas_per_sm);
   switch (optimizer) {
     case ACCEL_OPT_SGD: ps_apply_pull<OPT_SGD, 1><<<grid, 256, 0, s>>>(a); break;
@@ -428,7 +432,7 @@ int accel_shard_step(accel_ctx *ctx, const accel_peers *peers, int optimizer, fl
     const uint64_t n = begin + per <= shard ? per : shard - begin;
     // main stream: HBM-bound local sum + NVLink push of slice k ...
     rc = do_push(ctx, peers, grads, n_workers, grad_dtype, begin, n, s, &epoch,
-                 n_chunks > 1 ? 1 : 2);
+                 n_chunks > 1 ? 1 : 4);
     if (rc) return rc;
     ACCEL_CUDA(cudaEventRecord(ts->shard_ev_push, s));
     // ... while the auxiliary stream applies and broadcasts slice k-1 (NVLink-bound)

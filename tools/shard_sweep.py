@@ -53,6 +53,9 @@ def main():
             for pull in ("f32", "bf16"):
                 sps = ShardedPS(rank, world, local, elems, opt, pkg.HParams(lr=0.01), mode="fused",
                                 n_chunks=1, pull_dtype=pull)
+                if os.environ.get("SHARD_CTAS"):
+                    sps.ctx.set_kernel(ctas_per_sm=int(os.environ["SHARD_CTAS"]))
+                    row["ctas_per_sm"] = int(os.environ["SHARD_CTAS"])
                 g = [torch.randn(sps.padded, device=dev) * 0.01]
                 iters = 30 if mib <= 64 else 10
                 if pull == "f32":
