@@ -312,6 +312,39 @@ def run_sharded(args):
     dist.all_reduce(ms_t, op=dist.ReduceOp.MAX)
     ms = ms_t.item() / args.steps
     clk = clocks.stop() if rank == 0 else None
+
+    # ---- e2e: every rank's workers deliver their gradients in pinned HOST memory; per step each
+    # rank copies them in over its own PCIe link, runs the sharded step, and copies its updated
+    # replica back out. Wall clock, barrier on both sides, max over ranks.
+    e2e = None
+    if not args.no_e2e:
+        e2e_steps = max(1, min(args.steps, args.e2e_steps))
+        h_grads = [torch.empty(sps.padded, dtype=torch.float32).pin_memory() for _ in range(WORKERS)]
+        for h, g in zip(h_grads, grads):
+            h.copy_(g)
+        h_out = torch.empty(sps.padded, dtype=torch.float32).pin_memory()
+
+        def host_step():
+            for h, g in zip(h_grads, grads):
+                g.copy_(h, non_blocking=True)
+            sps.step(grads, stream)
+            h_out.copy_(sps.var, non_blocking=True)
+            torch.cuda.synchronize()
+        for _ in range(2):
+            host_step()
+        dist.barrier()
+        t0 = time.perf_counter()
+        for _ in range(e2e_steps):
+            host_step()
+        dist.barrier()
+        dt = torch.tensor([(time.perf_counter() - t0) / e2e_steps], device=dev)
+        dist.all_reduce(dt, op=dist.ReduceOp.MAX)
+        e2e = {"value": round(world * WORKERS * ELEMS * 4 / dt.item() / 1e9, 3), "unit": UNIT,
+               "h2d_bytes_per_step": world * WORKERS * sps.padded * 4,
+               "d2h_bytes_per_step": world * sps.padded * 4,
+               "ms_per_step": round(dt.item() * 1e3, 3), "steps": e2e_steps,
+               "path": "per rank: 8 pinned host gradients -> H2D over the rank's own PCIe link -> "
+                       "sharded fused step -> D2H of the updated replica"}
     if rank == 0:
         grad_bytes = world * WORKERS * ELEMS * 4
         peak, peak_src = peaks()
@@ -336,7 +369,7 @@ def run_sharded(args):
                          "note": "per-GPU HBM bytes of the whole step / step time",
                          "nvlink_gbs_per_gpu_per_dir": round(nvl_bytes / 2 / (ms * 1e-3) / 1e9, 2)},
             "cpu_baseline": None,
-            "e2e": None,
+            "e2e": e2e,
             "gpu_launches": args.steps * sps.launches_per_step,
             "clocks": clk,
         }
