@@ -45,6 +45,14 @@ __device__ __forceinline__ uint32_t ld_acquire_sys(const uint32_t *p) {
 __device__ __forceinline__ void st_release_sys(uint32_t *p, uint32_t v) {
   asm volatile("st.release.sys.global.u32 [%0], %1;" ::"l"(p), "r"(v) : "memory");
 }
+__device__ __forceinline__ uint32_t ld_relaxed_sys(const uint32_t *p) {
+  uint32_t v;
+  asm volatile("ld.relaxed.sys.global.u32 %0, [%1];" : "=r"(v) : "l"(p) : "memory");
+  return v;
+}
+__device__ __forceinline__ void st_relaxed_sys(uint32_t *p, uint32_t v) {
+  asm volatile("st.relaxed.sys.global.u32 [%0], %1;" ::"l"(p), "r"(v) : "memory");
+}
 __device__ __forceinline__ unsigned long long globaltimer_ns() {
   unsigned long long t;
   asm volatile("mov.u64 %0, %globaltimer;" : "=l"(t));
@@ -60,17 +68,19 @@ __device__ inline bool wait_all(uint32_t *flags, int base, int world, uint32_t e
     ok = 1;
     const unsigned long long t0 = globaltimer_ns();
     for (int s = 0; s < world && ok; ++s) {
-      // epochs only grow; signed distance handles the 32-bit wrap
-      while (static_cast<int32_t>(ld_acquire_sys(flags + base + s) - epoch) < 0) {
-        if (globaltimer_ns() - t0 > kSpinTimeoutNs || ld_acquire_sys(flags + kFlagStatus) != 0) {
+      // epochs only grow; signed distance handles the 32-bit wrap. Relaxed polls, then ONE
+      // system-scope fence below turns the observations into an acquire.
+      while (static_cast<int32_t>(ld_relaxed_sys(flags + base + s) - epoch) < 0) {
+        if (globaltimer_ns() - t0 > kSpinTimeoutNs || ld_relaxed_sys(flags + kFlagStatus) != 0) {
           atomicCAS(flags + kFlagStatus, 0u, 1u | (static_cast<uint32_t>(s) << 8) |
                                                  (static_cast<uint32_t>(base) << 16));
           ok = 0;
           break;
         }
-        __nanosleep(200);
+        __nanosleep(100);
       }
     }
+    __threadfence_system();
   }
   __syncthreads();
   return ok != 0;
@@ -87,7 +97,8 @@ __device__ inline void signal_all(const ShardArgs &a, int ticket_word, int word_
     if (done == gridDim.x - 1) {
       local[ticket_word] = 0;  // ready for the next launch
       __threadfence_system();  // all CTAs' tickets (and their stores) happen-before the flags
-      for (int p = 0; p < a.world; ++p) st_release_sys(a.flags[p] + word_base + a.rank, a.epoch);
+      // one fence, then relaxed stores: a release per peer would pay the fence `world` times
+      for (int p = 0; p < a.world; ++p) st_relaxed_sys(a.flags[p] + word_base + a.rank, a.epoch);
     }
   }
 }

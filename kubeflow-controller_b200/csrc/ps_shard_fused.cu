@@ -42,7 +42,8 @@ __device__ inline bool poll_all(uint32_t *flags, int base, int world, uint32_t t
   if (threadIdx.x == 0) {
     int ok = 1;
     for (int s = 0; s < world; ++s)
-      ok &= static_cast<int32_t>(ld_acquire_sys(flags + base + s) - target) >= 0;
+      ok &= static_cast<int32_t>(ld_relaxed_sys(flags + base + s) - target) >= 0;
+    if (ok) __threadfence_system();   // the relaxed observations become an acquire
     ready = ok;
   }
   __syncthreads();
@@ -176,7 +177,7 @@ __global__ void __launch_bounds__(kFusedThreads, 2)
         flags[kFlagSliceTicket + k] = 0;
         __threadfence_system();
         for (int p = 0; p < a.world; ++p)
-          st_release_sys(a.flags[p] + kFlagPush + a.rank, fa.epoch_base + k + 1);
+          st_relaxed_sys(a.flags[p] + kFlagPush + a.rank, fa.epoch_base + k + 1);
       }
     }
     // whatever has already arrived from everybody gets applied now, without waiting
@@ -201,7 +202,7 @@ __global__ void __launch_bounds__(kFusedThreads, 2)
       flags[kFlagTicketApply] = 0;
       __threadfence_system();
       for (int p = 0; p < a.world; ++p)
-        st_release_sys(a.flags[p] + kFlagPull + a.rank, fa.epoch_base + S);
+        st_relaxed_sys(a.flags[p] + kFlagPull + a.rank, fa.epoch_base + S);
     }
   }
   __syncthreads();
