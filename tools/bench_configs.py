@@ -111,6 +111,30 @@ def main():
                           "workers": workers, "elems": n, "us_per_step": round(dt * 1e6, 1),
                           "steps_per_s": round(1 / dt, 1),
                           "reference_doc_log_global_steps_per_s": 356}), flush=True)
+    # the sum-of-squares pre-pass of global-norm clipping (reads the N gradients once)
+    for bf16 in (False, True):
+        n, workers = 100_000_000, 8
+        g = [(torch.randn(n, device="cuda:0") * 0.01).to(torch.bfloat16 if bf16 else torch.float32)
+             for _ in range(workers)]
+        out = torch.zeros(1, device="cuda:0")
+        st = torch.cuda.current_stream()
+        for _ in range(3):
+            ctx.grad_sumsq(g, out, stream=st)
+        ts = []
+        for _ in range(10):
+            a, b = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+            a.record(st)
+            ctx.grad_sumsq(g, out, stream=st)
+            b.record(st)
+            torch.cuda.synchronize()
+            ts.append(a.elapsed_time(b))
+        ts.sort()
+        alg = n * workers * (2 if bf16 else 4)
+        print(json.dumps({"case": "sumsq 8x100M", "grad": "bf16" if bf16 else "f32",
+                          "ms_median": round(ts[5], 4), "hbm_gbs": round(alg / ts[5] / 1e6, 1),
+                          "frac_of_measured_peak": round(alg / ts[5] / 1e6 / pk, 4)}), flush=True)
+        del g
+        torch.cuda.empty_cache()
     for label, opt, bf16, workers, n in cases:
         r = run(ctx, opt, bf16, workers, n, 7 if n > (1 << 26) else 15, flush)
         r.update({"case": label, "opt": names[opt], "grad": "bf16" if bf16 else "f32",
