@@ -291,6 +291,18 @@ def grad_sumsq_static(grads, out, aggregate=AGG_SUM, count=None, stream=None) ->
                                                  _stream_handle(stream)))
 
 
+def host_register(array) -> None:
+    """Page-lock a host buffer (numpy array or CPU tensor) so ps_step_host copies at PCIe rate."""
+    ptr, nbytes = (array.ctypes.data, array.nbytes) if hasattr(array, "ctypes") \
+        else (array.data_ptr(), array.numel() * array.element_size())
+    check(load_library().accel_host_register(ptr, nbytes))
+
+
+def host_unregister(array) -> None:
+    ptr = array.ctypes.data if hasattr(array, "ctypes") else array.data_ptr()
+    check(load_library().accel_host_unregister(ptr))
+
+
 def adam_advance(hp: HParams) -> None:
     check(load_library().accel_adam_advance(ctypes.byref(hp)))
 

@@ -58,6 +58,14 @@ class DevBuffer:
                 self.lib.accel_dev_free(self.ptr)
             self.ptr = None
 
+    def __del__(self):
+        # views keep a reference to their DevBuffer (t._accel_owner), so this runs only once
+        # no tensor over the allocation is alive
+        try:
+            self.free()
+        except Exception:
+            pass
+
 
 def open_peer(handle: bytes) -> int:
     h = accel.IpcHandle()

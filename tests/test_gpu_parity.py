@@ -362,3 +362,24 @@ def test_checkpoint_restore_resumes_bit_exact(pkg, tmp_path):
         b.apply_gradients(g)
     assert torch.equal(a.var, b.var) and torch.equal(a.slot0, b.slot0) and torch.equal(a.slot1, b.slot1)
     assert a.hp.beta2_power == b.hp.beta2_power and b.global_step == 6
+
+
+def test_host_step_with_registered_numpy_buffers(pkg, ctx):
+    """Gradients living in ordinary (numpy) host memory, page-locked through the ABI."""
+    n, workers = 300_000, 3
+    var, _, _, grads = _inputs(n, workers, False, seed=21)
+    out = np.empty(n, F)
+    for a in grads + [out]:
+        pkg.accel.host_register(a)
+    try:
+        d_var = _to_dev(var)
+        arr = (ctypes.c_void_p * workers)(*[g.ctypes.data for g in grads])
+        hp = pkg.HParams(lr=0.01)
+        pkg.accel.check(pkg.load_library().accel_ps_step_host(
+            ctx.handle, 0, pkg.OPT_SGD, d_var.data_ptr(), None, None, arr, workers, pkg.F32, n,
+            ctypes.byref(hp), out.ctypes.data))
+        O.numpy_ps_step(O.SGD, var, None, None, grads, O.HParams(lr=0.01))
+        assert np.array_equal(out, var)
+    finally:
+        for a in grads + [out]:
+            pkg.accel.host_unregister(a)
