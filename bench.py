@@ -352,7 +352,8 @@ def run_sharded(args):
         # per GPU: read 8 local gradients + write partial (push), read `world` slots + var r/w
         # (apply), write the full replica (pull)
         hbm_bytes = sps.padded * (WORKERS * 4 + 4) + shard * (world * 4 + 8) + sps.padded * 4
-        nvl_bytes = 2 * (world - 1) * shard * 4          # push out + pull out, per GPU
+        pull_b = 2 if args.pull == "bf16" else 4
+        nvl_bytes = (world - 1) * shard * (4 + pull_b)   # push out + pull out, per GPU per direction
         line = {
             "metric": METRIC, "value": round(grad_bytes / (ms * 1e-3) / 1e9, 2), "unit": UNIT,
             "n_gpus": world, "steps": args.steps, "warmup": args.warmup,
@@ -366,8 +367,16 @@ def run_sharded(args):
                          "peak": peak, "unit": "GB/s",
                          "frac": round(hbm_bytes / (ms * 1e-3) / 1e9 / peak, 4), "traffic": None,
                          "peak_source": peak_src,
-                         "note": "per-GPU HBM bytes of the whole step / step time",
-                         "nvlink_gbs_per_gpu_per_dir": round(nvl_bytes / 2 / (ms * 1e-3) / 1e9, 2)},
+                         "note": "per-GPU HBM bytes of the whole step / step time; at N > 1 the step "
+                                 "is NVLink-bound as well, see `nvlink`"},
+            "nvlink": {"bytes_per_gpu_per_dir_per_step": nvl_bytes,
+                       "achieved": round(nvl_bytes / (ms * 1e-3) / 1e9, 2),
+                       "peak": 770.0, "unit": "GB/s per direction per GPU",
+                       "frac": round(nvl_bytes / (ms * 1e-3) / 1e9 / 770.0, 4),
+                       "frac_of_nominal_900": round(nvl_bytes / (ms * 1e-3) / 1e9 / 900.0, 4),
+                       "peak_source": "measured peer copy, B200_PROFILING.md",
+                       "note": "push sends (P-1)/P of the arena and the pull another (P-1)/P, in "
+                               "each direction, over the whole step time"},
             "cpu_baseline": None,
             "e2e": e2e,
             "gpu_launches": args.steps * sps.launches_per_step,

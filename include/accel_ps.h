@@ -283,6 +283,26 @@ int accel_tfjob_action(int worker_replicas, int ps_replicas, int succeeded_worke
  * spec order. Returns 1 / 0, or a negative status. */
 int accel_tfjob_is_local_job(const int *replica_types, int n);
 
+/* One whole sync of a distributed TFJob, as manageTFJob runs it
+ * (pkg/controller/controller.go:369-425): NewDistributedJob, Action(), then the
+ * events in list order — GetService(type, i) per service, GetSpec(type, i) per
+ * pod, indices restarting at 0 for however many are missing — with the random
+ * 5-character tails taken from `suffixes` in the order the reference draws
+ * them (compose()'s RuntimeID first when it runs, then one per Service).
+ * runtime_id_in is the job's stored Spec.RuntimeID (used when compose() does
+ * not run). The result is text, one record per line, fields TAB-separated:
+ *   runtime_id <TAB> <id after the sync>
+ *   event <TAB> <ActionType> <TAB> <number>
+ *   service <TAB> <generated name> <TAB> <k=v,k=v,... labels sorted by key>
+ *   pod <TAB> <PS|Worker> <TAB> <index> <TAB> <labels> <TAB> <arg0> <TAB> <arg1> <TAB> <arg2> <TAB> <arg3>
+ *   template <TAB> <PS|Worker> <TAB> <labels left in the shared template> <TAB> <args left in it>
+ * (the `template` lines show the in-place mutation of GetSpec, distributed.go:118-124).
+ * Returns bytes written excluding the NUL, or a negative status. */
+int accel_tfjob_sync_plan(const char *job_name, const char *runtime_id_in, int worker_replicas,
+                          int ps_replicas, int succeeded_workers, int worker_services,
+                          int ps_services, int active_workers, int active_ps,
+                          const char *const *suffixes, int n_suffixes, char *buf, size_t buflen);
+
 /* "<job>-<type lower-cased>-<index>" — DistributedJob.getServiceName
  * (pkg/tensorflow/distributed.go:161-163). Returns the length written
  * (excluding NUL) or a negative accel_status. */

@@ -29,7 +29,8 @@ SYMBOLS = [
     "accel_ctx_gpu_of", "accel_ctx_set_kernel", "accel_plan_flat", "accel_plan_round_robin",
     "accel_apply_sgd", "accel_apply_momentum", "accel_apply_adam", "accel_adam_advance",
     "accel_grad_sumsq", "accel_grad_sumsq_static", "accel_ps_step_host", "accel_host_register", "accel_host_unregister",
-    "accel_tfjob_action", "accel_tfjob_is_local_job", "accel_tfjob_service_key", "accel_tfjob_cluster_spec",
+    "accel_tfjob_action", "accel_tfjob_is_local_job", "accel_tfjob_sync_plan",
+    "accel_tfjob_service_key", "accel_tfjob_cluster_spec",
     "accel_tfjob_labels", "accel_tfjob_parse_argv", "accel_ipc_export", "accel_ipc_open",
     "accel_ipc_close", "accel_dev_alloc", "accel_dev_free", "accel_shard_push",
     "accel_shard_apply_pull", "accel_shard_wait_push", "accel_shard_wait_pull", "accel_shard_step", "accel_shard_step_fused",
@@ -138,6 +139,8 @@ def load_library() -> ctypes.CDLL:
                                          u64, u64, u32, vp]
     L.accel_shard_wait_pull.argtypes = [vp, ctypes.POINTER(Peers), u32, vp]
     L.accel_shard_wait_push.argtypes = [vp, ctypes.POINTER(Peers), u32, vp]
+    L.accel_tfjob_sync_plan.argtypes = [ctypes.c_char_p, ctypes.c_char_p] + [i32] * 7 + \
+        [ctypes.POINTER(ctypes.c_char_p), i32, ctypes.c_char_p, ctypes.c_size_t]
     L.accel_tfjob_is_local_job.argtypes = [ctypes.POINTER(i32), i32]
     L.accel_shard_step.argtypes = [vp, ctypes.POINTER(Peers), i32, vp, vp, pvp, i32, i32, i32, php,
                                    vp, i32, vp]

@@ -9,18 +9,19 @@
 
 namespace accel {
 
-// Registers are the budget: keep (gradient + state) values in flight per thread
-// at or below ~92 fp32 so nothing spills under __launch_bounds__(512) (128 regs).
-constexpr int max_unroll(int nw_in_flight, int ve, int slots) {
-  int per_u = (nw_in_flight + 1 + slots) * ve;
+// Registers are the budget: keep (packed gradient + state) registers in flight per thread
+// at or below ~92 so nothing spills under __launch_bounds__(512) (128 regs).
+constexpr int max_unroll(int nw_in_flight, int r, int ve, int slots) {
+  int per_u = nw_in_flight * r + (1 + slots) * ve;
   int u = 92 / per_u;
   return u >= 4 ? 4 : (u >= 2 ? 2 : 1);
 }
 
 template <int OPT, typename G, int NW, bool WIDE, int U>
 static int launch_one(const ApplyArgs &a, const LaunchShape &ls, cudaStream_t stream) {
-  constexpr int VE = Item<G, WIDE>::VE;
-  constexpr int kMaxU = max_unroll(NW > 0 ? NW : 6, VE, OptTraits<OPT>::kSlots);
+  constexpr int VE = ApplyItem<G, WIDE, OPT>::VE;
+  constexpr int kMaxU =
+      max_unroll(NW > 0 ? NW : 6, ApplyItem<G, WIDE, OPT>::R, VE, OptTraits<OPT>::kSlots);
   if constexpr (U > kMaxU) {
     return launch_one<OPT, G, NW, WIDE, (U > 1 ? U / 2 : 1)>(a, ls, stream);
   } else {

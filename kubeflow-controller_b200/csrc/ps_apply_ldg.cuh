@@ -19,7 +19,8 @@ namespace accel {
 template <int OPT, typename G, int NW, bool WIDE, int U>
 __global__ void __launch_bounds__(512)
     ps_apply_ldg(const __grid_constant__ ApplyArgs a) {
-  constexpr int VE = Item<G, WIDE>::VE;
+  constexpr int VE = ApplyItem<G, WIDE, OPT>::VE;
+  constexpr int R = ApplyItem<G, WIDE, OPT>::R;
   constexpr int SLOTS = OptTraits<OPT>::kSlots;
   const Scalars sc = make_scalars(a);
 
@@ -39,12 +40,12 @@ __global__ void __launch_bounds__(512)
 
     float acc[U][VE];
     if constexpr (NW > 0) {
-      float g[NW][U][VE];
+      uint32_t g[NW][U][R];   // packed: bf16 gradients are widened only when they are added
 #pragma unroll
       for (int w = 0; w < NW; ++w)
 #pragma unroll
         for (int j = 0; j < U; ++j)
-          if (ok[j]) load_grad_item<G, WIDE>(a.grad[w], idx[j], g[w][j]);
+          if (ok[j]) load_grad_raw<R>(a.grad[w], idx[j], g[w][j]);
       float v[U][VE], s0[U][VE], s1[U][VE];
 #pragma unroll
       for (int j = 0; j < U; ++j) {
@@ -59,9 +60,9 @@ __global__ void __launch_bounds__(512)
         if (!ok[j]) continue;
 #pragma unroll
         for (int e = 0; e < VE; ++e) {
-          float sum = g[0][j][e];
+          float sum = grad_elem<G>(g[0][j], e);
 #pragma unroll
-          for (int w = 1; w < NW; ++w) sum = __fadd_rn(sum, g[w][j][e]);
+          for (int w = 1; w < NW; ++w) sum = __fadd_rn(sum, grad_elem<G>(g[w][j], e));
           update<OPT>(v[j][e], s0[j][e], s1[j][e], finish_grad(sum, sc), sc);
         }
         store_state_item<VE, WIDE>(a.var, idx[j], v[j]);
@@ -81,13 +82,13 @@ __global__ void __launch_bounds__(512)
       }
       const int n = a.n_workers;
       for (int w0 = 0; w0 < n; w0 += 4) {
-        float g[4][U][VE];
+        uint32_t g[4][U][R];
 #pragma unroll
         for (int k = 0; k < 4; ++k)
           if (w0 + k < n)
 #pragma unroll
             for (int j = 0; j < U; ++j)
-              if (ok[j]) load_grad_item<G, WIDE>(a.grad[w0 + k], idx[j], g[k][j]);
+              if (ok[j]) load_grad_raw<R>(a.grad[w0 + k], idx[j], g[k][j]);
 #pragma unroll
         for (int k = 0; k < 4; ++k)
           if (w0 + k < n)
@@ -95,7 +96,8 @@ __global__ void __launch_bounds__(512)
             for (int j = 0; j < U; ++j)
 #pragma unroll
               for (int e = 0; e < VE; ++e)
-                acc[j][e] = (w0 + k == 0) ? g[k][j][e] : __fadd_rn(acc[j][e], g[k][j][e]);
+                acc[j][e] = (w0 + k == 0) ? grad_elem<G>(g[k][j], e)
+                                          : __fadd_rn(acc[j][e], grad_elem<G>(g[k][j], e));
       }
 #pragma unroll
       for (int j = 0; j < U; ++j) {

@@ -37,14 +37,6 @@ struct ShardArgs {
   float lr, momentum, beta1, one_minus_beta1, one_minus_beta2, alpha, epsilon, mean_div, clip_norm;
 };
 
-__device__ __forceinline__ uint32_t ld_acquire_sys(const uint32_t *p) {
-  uint32_t v;
-  asm volatile("ld.acquire.sys.global.u32 %0, [%1];" : "=r"(v) : "l"(p) : "memory");
-  return v;
-}
-__device__ __forceinline__ void st_release_sys(uint32_t *p, uint32_t v) {
-  asm volatile("st.release.sys.global.u32 [%0], %1;" ::"l"(p), "r"(v) : "memory");
-}
 __device__ __forceinline__ uint32_t ld_relaxed_sys(const uint32_t *p) {
   uint32_t v;
   asm volatile("ld.relaxed.sys.global.u32 %0, [%1];" : "=r"(v) : "l"(p) : "memory");

@@ -315,6 +315,74 @@ int accel_tfjob_is_local_job(const int *replica_types, int n) {
   return tfjob::IsLocalJob(job) ? 1 : 0;
 }
 
+int accel_tfjob_sync_plan(const char *job_name, const char *runtime_id_in, int worker_replicas,
+                          int ps_replicas, int succeeded_workers, int worker_services,
+                          int ps_services, int active_workers, int active_ps,
+                          const char *const *suffixes, int n_suffixes, char *buf, size_t buflen) {
+  if (!job_name) return fail(ACCEL_ERR_INVALID, "job_name is NULL");
+  if (n_suffixes < 0 || (n_suffixes > 0 && !suffixes))
+    return fail(ACCEL_ERR_INVALID, "suffixes is NULL");
+  std::vector<std::string> sfx;
+  for (int i = 0; i < n_suffixes; ++i) {
+    if (!suffixes[i] || strlen(suffixes[i]) != tfjob::kRandomLength)
+      return fail(ACCEL_ERR_INVALID, "suffix %d must have exactly %d characters", i,
+                  tfjob::kRandomLength);
+    sfx.push_back(suffixes[i]);
+  }
+  auto fmt_labels = [](const std::map<std::string, std::string> &m) {
+    std::string s;
+    for (const auto &kv : m) s += (s.empty() ? "" : ",") + kv.first + "=" + kv.second;
+    return s;
+  };
+  auto join = [](const std::vector<std::string> &v, const char *sep) {
+    std::string s;
+    for (size_t i = 0; i < v.size(); ++i) s += (i ? sep : "") + v[i];
+    return s;
+  };
+  std::string out;
+  try {
+    tfjob::TFJob job = two_spec_job(job_name, ps_replicas, worker_replicas);
+    job.runtime_id = runtime_id_in ? runtime_id_in : "";
+    tfjob::FixedSuffixSource names(sfx);
+    tfjob::DistributedJob dj(&job, active_workers, active_ps, worker_services, ps_services,
+                             succeeded_workers, &names);
+    const std::vector<tfjob::Event> events = dj.Action();   // compose() happens in here
+    out += "runtime_id\t" + job.runtime_id + "\n";
+    for (const auto &e : events)
+      out += std::string("event\t") + tfjob::action_name(e.action) + "\t" +
+             std::to_string(e.number) + "\n";
+    for (const auto &e : events) {
+      tfjob::ReplicaType t = tfjob::ReplicaType::Worker;
+      bool service = false, pod = false;
+      switch (e.action) {
+        case tfjob::ActionType::ShouldAddWorkerService: service = true; break;
+        case tfjob::ActionType::ShouldAddPSService: service = true; t = tfjob::ReplicaType::PS; break;
+        case tfjob::ActionType::ShouldAddWorker: pod = true; break;
+        case tfjob::ActionType::ShouldAddPS: pod = true; t = tfjob::ReplicaType::PS; break;
+        default: break;
+      }
+      for (int i = 0; i < e.number; ++i) {
+        if (service) {
+          const tfjob::Service svc = dj.GetService(t, i);
+          out += "service\t" + svc.name + "\t" + fmt_labels(svc.labels) + "\n";
+        } else if (pod) {
+          const tfjob::ReplicaSpec *spec = dj.GetSpec(t, i);   // the pod copies the template NOW
+          out += std::string("pod\t") + tfjob::replica_type_name(t) + "\t" + std::to_string(i) +
+                 "\t" + fmt_labels(spec->template_labels) + "\t" +
+                 join(spec->container0_args, "\t") + "\n";
+        }
+      }
+    }
+    for (const auto &spec : job.specs)
+      out += std::string("template\t") + tfjob::replica_type_name(spec.type) + "\t" +
+             fmt_labels(spec.template_labels) + "\t" + join(spec.container0_args, " ") + "\n";
+  } catch (const std::exception &ex) {
+    // the Go code would panic here (index out of range) or block on its PRNG; report instead
+    return fail(ACCEL_ERR_INVALID, "%s", ex.what());
+  }
+  return copy_out(out, buf, buflen);
+}
+
 int accel_tfjob_service_key(const char *job_name, int replica_type, int index, char *buf,
                             size_t buflen) {
   tfjob::ReplicaType t;

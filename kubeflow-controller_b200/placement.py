@@ -34,6 +34,37 @@ def is_local_job(replica_types) -> bool:
     return bool(accel.check(L.accel_tfjob_is_local_job(arr, len(replica_types))))
 
 
+def sync_plan(job: str, runtime_id: str, workers: int, ps: int, suffixes, succeeded=0,
+              worker_services=0, ps_services=0, active_workers=0, active_ps=0):
+    """One sync of manageTFJob (pkg/controller/controller.go:369-425) ->
+    dict(runtime_id, events, services, pods, templates)."""
+    L = accel.load_library()
+    sfx = (ctypes.c_char_p * max(len(suffixes), 1))(*[s.encode() for s in suffixes])
+    buf = ctypes.create_string_buffer(1 << 18)
+    accel.check(L.accel_tfjob_sync_plan(job.encode(), runtime_id.encode(), workers, ps, succeeded,
+                                        worker_services, ps_services, active_workers, active_ps,
+                                        sfx, len(suffixes), buf, len(buf)))
+
+    def labels(s):
+        return dict(kv.split("=", 1) for kv in s.split(",")) if s else {}
+    plan = {"runtime_id": None, "events": [], "services": [], "pods": [], "templates": {}}
+    for line in buf.value.decode().splitlines():
+        f = line.split("\t")
+        if f[0] == "runtime_id":
+            plan["runtime_id"] = f[1] if len(f) > 1 else ""
+        elif f[0] == "event":
+            plan["events"].append((f[1], int(f[2])))
+        elif f[0] == "service":
+            plan["services"].append({"name": f[1], "labels": labels(f[2])})
+        elif f[0] == "pod":
+            plan["pods"].append({"type": f[1], "index": int(f[2]), "labels": labels(f[3]),
+                                 "args": f[4:8]})
+        elif f[0] == "template":
+            plan["templates"][f[1]] = {"labels": labels(f[2]),
+                                       "args": f[3].split(" ") if len(f) > 3 and f[3] else []}
+    return plan
+
+
 def service_key(job: str, typ: str, index: int) -> str:
     """getServiceName (distributed.go:161-163)."""
     L = accel.load_library()

@@ -85,3 +85,33 @@ def flat(n_elems: int, n_ps: int, align: int = 1):
     padded = -(-n_elems // unit) * unit
     per = padded // n_ps
     return [(r * per, per) for r in range(n_ps)], padded
+
+
+def sync_plan(job: str, runtime_id: str, workers: int, ps: int, suffixes, succeeded=0,
+              worker_services=0, ps_services=0, active_workers=0, active_ps=0):
+    """One sync of manageTFJob (pkg/controller/controller.go:369-425) restated: Action() runs to
+    completion first (compose() draws the RuntimeID), then events execute in order; GetService
+    draws one suffix each and records the name; GetSpec rewrites the shared template in place."""
+    sfx = list(suffixes)
+    events, composed = action(workers, ps, succeeded, worker_services, ps_services,
+                              active_workers, active_ps)
+    tmpl = {"PS": {"labels": {}, "args": []}, "Worker": {"labels": {}, "args": []}}
+    if composed:
+        runtime_id = generate_name("", sfx.pop(0))
+        for t in tmpl:
+            tmpl[t]["labels"] = labels(job, t, runtime_id)
+    names, services, pods = {}, [], []
+    for act, number in events:
+        typ = "PS" if "PS" in act else "Worker"
+        for i in range(number):
+            if act.endswith("Service"):
+                key = service_key(job, typ, i)
+                names[key] = generate_name(key + "-", sfx.pop(0))
+                services.append({"name": names[key], "labels": labels(job, typ, runtime_id, i)})
+            elif act in ("ShouldAddWorker", "ShouldAddPS"):
+                tmpl[typ]["labels"]["index"] = str(i)
+                tmpl[typ]["args"] = cluster_spec(job, workers, ps, names, typ, i)
+                pods.append({"type": typ, "index": i, "labels": dict(tmpl[typ]["labels"]),
+                             "args": list(tmpl[typ]["args"])})
+    return {"runtime_id": runtime_id, "events": events, "services": services, "pods": pods,
+            "templates": tmpl}

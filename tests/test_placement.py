@@ -202,3 +202,82 @@ def test_round_robin_on_named_models(pkg, name, n_ps):
 def test_is_local_job_table(P, first, second, want):
     specs = [first] + ([second] if second else [])
     assert P.is_local_job(specs) is want
+
+
+# ---- one whole sync: events executed in order, names recorded, templates mutated ------------
+SFX = ["bcdfg", "hjklm", "npqrs", "tvwxz", "24567", "89bcd", "fghjk", "lmnpq", "rstvw"]
+
+
+def test_first_sync_of_dist_yml(P):
+    """examples/tfjob/dist.yml, nothing exists yet: RuntimeID, 4+2 Services, 4+2 pods."""
+    plan = P.sync_plan("dist-training-job", "", 4, 2, SFX[:7])
+    assert plan == PO.sync_plan("dist-training-job", "", 4, 2, SFX[:7])
+    assert plan["runtime_id"] == "bcdfg"                    # compose() draws first
+    assert plan["events"] == [("ShouldAddWorkerService", 4), ("ShouldAddPSService", 2),
+                              ("ShouldAddWorker", 4), ("ShouldAddPS", 2)]
+    assert [s["name"] for s in plan["services"]] == [
+        "dist-training-job-worker-0-hjklm", "dist-training-job-worker-1-npqrs",
+        "dist-training-job-worker-2-tvwxz", "dist-training-job-worker-3-24567",
+        "dist-training-job-ps-0-89bcd", "dist-training-job-ps-1-fghjk"]
+    assert plan["services"][4]["labels"] == {
+        "kubeflow.caicloud.io": "true", "job_type": "PS", "runtime_id": "bcdfg",
+        "tf_job_name": "dist-training-job", "index": "0"}
+    ps1 = [p for p in plan["pods"] if p["type"] == "PS" and p["index"] == 1][0]
+    assert ps1["args"] == [
+        "--worker_hosts=dist-training-job-worker-0-hjklm:2222,dist-training-job-worker-1-npqrs:2222,"
+        "dist-training-job-worker-2-tvwxz:2222,dist-training-job-worker-3-24567:2222",
+        "--ps_hosts=dist-training-job-ps-0-89bcd:2222,dist-training-job-ps-1-fghjk:2222",
+        "--job_name=ps", "--task_index=1"]
+    assert ps1["labels"]["index"] == "1" and ps1["labels"]["job_type"] == "PS"
+    # GetSpec mutates the shared template: it is left carrying the LAST replica's index and args
+    assert plan["templates"]["Worker"]["labels"]["index"] == "3"
+    assert plan["templates"]["PS"]["args"][3] == "--task_index=1"
+
+
+def test_later_sync_recreates_pods_with_degenerate_hosts(P):
+    """Services exist, two workers died: no compose of names -> hosts are ":2222" (Appendix A.5),
+    the RuntimeID changes (compose runs whenever workers are missing), indices restart at 0."""
+    plan = P.sync_plan("dist-training-job", "oldid", 4, 2, ["zzzzz"[:5].replace("z", "b")],
+                       worker_services=4, ps_services=2, active_workers=2, active_ps=2)
+    assert plan == PO.sync_plan("dist-training-job", "oldid", 4, 2, ["bbbbb"],
+                                worker_services=4, ps_services=2, active_workers=2, active_ps=2)
+    assert plan["runtime_id"] == "bbbbb" and plan["services"] == []
+    assert [(p["type"], p["index"]) for p in plan["pods"]] == [("Worker", 0), ("Worker", 1)]
+    assert plan["pods"][0]["args"][0] == "--worker_hosts=:2222,:2222,:2222,:2222"
+    assert plan["pods"][0]["args"][1] == "--ps_hosts=:2222,:2222"
+
+
+def test_only_ps_missing_keeps_runtime_id(P):
+    plan = P.sync_plan("j", "keepme", 2, 2, [], worker_services=2, ps_services=2,
+                       active_workers=2, active_ps=1)
+    assert plan == PO.sync_plan("j", "keepme", 2, 2, [], worker_services=2, ps_services=2,
+                                active_workers=2, active_ps=1)
+    assert plan["runtime_id"] == "keepme"
+    assert plan["events"] == [("Nothing", 0), ("ShouldAddPS", 1)]
+    # no compose: the PS template has no base labels yet, only the index GetSpec adds
+    assert plan["pods"][0]["labels"] == {"index": "0"}
+
+
+def test_generated_names_are_truncated_to_63(P):
+    """simpleNameGenerator keeps at most 58 bytes of the base (generate.go:53-65)."""
+    job = "x" * 70
+    plan = P.sync_plan(job, "", 1, 1, SFX[:3])
+    assert plan == PO.sync_plan(job, "", 1, 1, SFX[:3])
+    for s in plan["services"]:
+        assert len(s["name"]) == 63 and s["name"].startswith("x" * 58)
+
+
+@pytest.mark.parametrize("w,p,succ,wsvc,psvc,aw,ap", [
+    (4, 2, 0, 0, 0, 0, 0), (4, 2, 1, 4, 2, 1, 2), (3, 1, 0, 0, 1, 3, 0), (2, 2, 0, 2, 0, 0, 0),
+    (1, 1, 0, 0, 0, 1, 1), (8, 8, 0, 0, 0, 0, 0), (0, 0, 0, 0, 0, 0, 0)])
+def test_sync_plan_matches_restatement(P, w, p, succ, wsvc, psvc, aw, ap):
+    sfx = (SFX * 3)[:1 + w + p]
+    kw = dict(succeeded=succ, worker_services=wsvc, ps_services=psvc, active_workers=aw, active_ps=ap)
+    assert P.sync_plan("job", "rid00", w, p, sfx, **kw) == PO.sync_plan("job", "rid00", w, p, sfx, **kw)
+
+
+def test_sync_plan_errors(P, pkg):
+    with pytest.raises(pkg.AccelError, match="exhausted"):
+        P.sync_plan("j", "", 2, 1, SFX[:2])          # needs 1 + 2 + 1 suffixes
+    with pytest.raises(pkg.AccelError, match="5 characters"):
+        P.sync_plan("j", "", 1, 1, ["abc", "bcdfg", "bcdfg"])
