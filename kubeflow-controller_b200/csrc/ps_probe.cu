@@ -7,6 +7,7 @@ namespace accel {
 // mode 0: multimem.st of this rank's shard through the multicast mapping (all-gather pattern)
 // mode 1: multimem.ld_reduce of this rank's shard (in-switch sum over all ranks), result to `local`
 // mode 2: plain local copy of the shard (HBM reference)
+// mode 3 / 4: unicast peer load / peer store of the same bytes (`mc` = the peer's buffer)
 template <int MODE>
 __global__ void __launch_bounds__(256) ps_probe_multimem(float *mc, float *local, uint64_t shard_off,
                                                          uint64_t n_vec4) {
@@ -25,9 +26,17 @@ __global__ void __launch_bounds__(256) ps_probe_multimem(float *mc, float *local
                    : "l"(p)
                    : "memory");
       st_state_128(local + i * 4, v);
-    } else {
+    } else if constexpr (MODE == 2) {
       ld_state_128(local + i * 4, v);
       st_state_128(local + n_vec4 * 4 + i * 4, v);
+    } else if constexpr (MODE == 3) {
+      // unicast peer LOAD: `mc` is a peer's buffer here; read its shard, store locally
+      ld_state_128(p, v);
+      st_state_128(local + i * 4, v);
+    } else {
+      // unicast peer STORE: read locally, store into the peer's buffer
+      ld_state_128(local + i * 4, v);
+      st_state_128(p, v);
     }
   }
 }
@@ -42,6 +51,8 @@ extern "C" int accel_dev_probe_multimem(float *mc, float *local, uint64_t shard_
   switch (mode) {
     case 0: ps_probe_multimem<0><<<ctas, 256, 0, s>>>(mc, local, shard_off_elems, n4); break;
     case 1: ps_probe_multimem<1><<<ctas, 256, 0, s>>>(mc, local, shard_off_elems, n4); break;
+    case 3: ps_probe_multimem<3><<<ctas, 256, 0, s>>>(mc, local, shard_off_elems, n4); break;
+    case 4: ps_probe_multimem<4><<<ctas, 256, 0, s>>>(mc, local, shard_off_elems, n4); break;
     default: ps_probe_multimem<2><<<ctas, 256, 0, s>>>(mc, local, shard_off_elems, n4); break;
   }
   ACCEL_CUDA(cudaGetLastError());

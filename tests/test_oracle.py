@@ -171,3 +171,44 @@ def test_golden_fixture_regression():
         assert np.array_equal(var, z[f"{name}.var_out"])
         assert np.array_equal(s0, z[f"{name}.s0_out"])
         assert np.array_equal(s1, z[f"{name}.s1_out"])
+
+
+def test_nesterov_momentum_cross_check_torch_sgd():
+    """TF: var -= g*lr + accum*momentum*lr (accum already updated); torch nesterov:
+    p -= lr*(g + momentum*buf). Same mathematics, different rounding order."""
+    rng = np.random.default_rng(17)
+    n = 8_000
+    var = rng.standard_normal(n).astype(F)
+    p = torch.nn.Parameter(torch.from_numpy(var.copy()))
+    opt = torch.optim.SGD([p], lr=0.05, momentum=0.9, nesterov=True)
+    acc = np.zeros(n, F)
+    for _ in range(6):
+        g = (0.01 * rng.standard_normal(n)).astype(F)
+        p.grad = torch.from_numpy(g.copy())
+        opt.step()
+        O.numpy_ps_step(O.MOMENTUM, var, acc, None, [g],
+                        O.HParams(lr=0.05, momentum=0.9, use_nesterov=True))
+    np.testing.assert_allclose(var, p.detach().numpy(), rtol=1e-5, atol=1e-6)
+
+
+def test_adam_cross_check_torch_adam_with_zero_epsilon():
+    """With epsilon = 0 TF's 'epsilon-hat' form and torch.optim.Adam's form are the same
+    mathematics (they differ only in where epsilon enters), so torch serves as an independent
+    implementation of m, v, the bias corrections and the beta-power bookkeeping."""
+    rng = np.random.default_rng(19)
+    n = 6_000
+    var = rng.standard_normal(n).astype(F)
+    p = torch.nn.Parameter(torch.from_numpy(var.copy()))
+    opt = torch.optim.Adam([p], lr=0.01, betas=(0.9, 0.999), eps=0.0)
+    m, v = np.zeros(n, F), np.zeros(n, F)
+    hp = O.HParams(lr=0.01, epsilon=0.0)
+    for _ in range(15):
+        g = (0.01 * rng.standard_normal(n) + 0.02).astype(F)
+        p.grad = torch.from_numpy(g.copy())
+        opt.step()
+        O.numpy_ps_step(O.ADAM, var, m, v, [g], hp)
+        hp.advance()
+    np.testing.assert_allclose(var, p.detach().numpy(), rtol=2e-5, atol=2e-6)
+    state = opt.state[p]
+    np.testing.assert_allclose(m, state["exp_avg"].numpy(), rtol=1e-5, atol=1e-8)
+    np.testing.assert_allclose(v, state["exp_avg_sq"].numpy(), rtol=1e-5, atol=1e-10)

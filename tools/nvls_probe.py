@@ -33,11 +33,14 @@ def main():
         return
     loc = torch.randn(2 * shard, device=dev)
     stream = torch.cuda.current_stream()
-    for mode, name in ((2, "local copy"), (0, "multimem.st (all-gather)"),
+    peer = buf.peer_ptrs[(rank + 1) % world]
+    for mode, name in ((2, "local copy"), (3, "peer load (right neighbour)"),
+                       (4, "peer store (right neighbour)"), (0, "multimem.st (all-gather)"),
                        (1, "multimem.ld_reduce (reduce-scatter)")):
-        for ctas in (148, 296, 592, 1184):
+        for ctas in (296, 592, 1184):
             def go():
-                pkg.accel.check(fn(buf.multicast_ptr, loc.data_ptr(), rank * shard, shard, mode,
+                base = peer if mode in (3, 4) else buf.multicast_ptr
+                pkg.accel.check(fn(base, loc.data_ptr(), rank * shard, shard, mode,
                                    ctas, stream.cuda_stream))
             for _ in range(3):
                 go()
