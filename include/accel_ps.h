@@ -185,6 +185,23 @@ int accel_apply_adam(accel_ctx *ctx, int task, float *var, float *m, float *v,
  * run once per step after all ApplyAdam ops (mnist_replica.py:170,184). */
 int accel_adam_advance(accel_hparams *hp);
 
+/* Optimizer state that advances ON THE DEVICE (SURVEY §8 f, rank 2): a 16-byte,
+ * 16-byte-aligned, caller-owned device block {float beta1_power, float
+ * beta2_power, uint64 global_step}. accel_opt_state_init fills it from hp's
+ * powers; accel_apply_dev_state is accel_apply_sgd/_momentum/_adam with Adam's
+ * alpha computed in the kernel from the device powers (hp's powers are
+ * ignored; same fp32 operations as the host form, so results are identical)
+ * followed on the same stream by TF's finish step — powers *= betas (Adam),
+ * global_step += 1 (the increment of mnist_replica.py:142,184). Nothing in a
+ * step depends on host-side mutable state, so a step can be recorded once and
+ * replayed. slot0/slot1 are ignored where the optimizer has no such slot. */
+int accel_opt_state_init(void *dev_state, const accel_hparams *hp, uint64_t global_step,
+                         accel_stream_t stream);
+int accel_apply_dev_state(accel_ctx *ctx, int task, int optimizer, float *var, float *slot0,
+                          float *slot1, const void *const *grads, int n_workers, int grad_dtype,
+                          uint64_t count, const accel_hparams *hp, const float *grad_sumsq_dev,
+                          void *dev_state, accel_stream_t stream);
+
 /* out_sumsq_dev[0] = sum over [0,count) of G^2, G = aggregate(grads), for
  * tf.clip_by_global_norm. Deterministic for a given launch
  * shape: per-thread fp32, warp-shuffle + shared-memory tree per CTA, CTA

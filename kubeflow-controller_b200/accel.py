@@ -28,6 +28,7 @@ SYMBOLS = [
     "accel_version", "accel_last_error", "accel_ctx_create", "accel_ctx_destroy",
     "accel_ctx_gpu_of", "accel_ctx_set_kernel", "accel_plan_flat", "accel_plan_round_robin",
     "accel_apply_sgd", "accel_apply_momentum", "accel_apply_adam", "accel_adam_advance",
+    "accel_opt_state_init", "accel_apply_dev_state",
     "accel_grad_sumsq", "accel_grad_sumsq_static", "accel_ps_step_host", "accel_host_register", "accel_host_unregister",
     "accel_tfjob_action", "accel_tfjob_is_local_job", "accel_tfjob_sync_plan",
     "accel_tfjob_service_key", "accel_tfjob_cluster_spec",
@@ -113,6 +114,8 @@ def load_library() -> ctypes.CDLL:
     L.accel_apply_momentum.argtypes = [vp, i32, vp, vp, pvp, i32, i32, u64, php, vp, vp]
     L.accel_apply_adam.argtypes = [vp, i32, vp, vp, vp, pvp, i32, i32, u64, php, vp, vp]
     L.accel_adam_advance.argtypes = [php]
+    L.accel_opt_state_init.argtypes = [vp, php, u64, vp]
+    L.accel_apply_dev_state.argtypes = [vp, i32, i32, vp, vp, vp, pvp, i32, i32, u64, php, vp, vp, vp]
     L.accel_grad_sumsq.argtypes = [vp, i32, pvp, i32, i32, u64, i32, vp, vp]
     L.accel_grad_sumsq_static.argtypes = [pvp, i32, i32, u64, i32, vp, vp]
     L.accel_ps_step_host.argtypes = [vp, i32, i32, vp, vp, vp, pvp, i32, i32, u64, php, vp]
@@ -264,6 +267,19 @@ class Context:
         if optimizer == OPT_ADAM:
             return self.apply_adam(var, slot0, slot1, grads, hp, **kw)
         raise ValueError(f"unknown optimizer {optimizer}")
+
+    def opt_state_init(self, dev_state, hp: HParams, global_step=0, stream=None):
+        """dev_state: a CUDA tensor of 4 float32 (16 bytes): beta powers + uint64 global step."""
+        check(self.lib.accel_opt_state_init(_ptr(dev_state), ctypes.byref(hp), global_step,
+                                            _stream_handle(stream)))
+
+    def apply_dev_state(self, optimizer, var, slot0, slot1, grads, hp: HParams, dev_state, task=0,
+                        count=None, sumsq=None, stream=None):
+        n = var.numel() if count is None else count
+        check(self.lib.accel_apply_dev_state(self.handle, task, optimizer, _ptr(var), _ptr(slot0),
+                                             _ptr(slot1), _grad_array(grads), len(grads),
+                                             _grad_dtype(grads[0]), n, ctypes.byref(hp),
+                                             _ptr(sumsq), _ptr(dev_state), _stream_handle(stream)))
 
     def grad_sumsq(self, grads, out, aggregate=AGG_SUM, task=0, count=None, stream=None):
         n = grads[0].numel() if count is None else count

@@ -138,7 +138,7 @@ static int build_args(int optimizer, float *var, float *slot0, float *slot1,
 static int apply_common(accel_ctx *ctx, int task, int optimizer, float *var, float *slot0,
                         float *slot1, const void *const *grads, int n_workers, int grad_dtype,
                         uint64_t count, const accel_hparams *hp, const float *sumsq_dev,
-                        accel_stream_t stream) {
+                        accel_stream_t stream, const float *dev_powers = nullptr) {
   TaskState *ts = nullptr;
   int rc = task_state(ctx, task, &ts);
   if (rc) return rc;
@@ -147,6 +147,7 @@ static int apply_common(accel_ctx *ctx, int task, int optimizer, float *var, flo
                   ctx->tuning.kernel, &a);
   if (rc) return rc;
   if (count == 0) return ACCEL_OK;
+  a.dev_powers = optimizer == ACCEL_OPT_ADAM ? dev_powers : nullptr;
   cudaStream_t s = static_cast<cudaStream_t>(stream);
   if (a.clip_norm > 0.0f && a.sumsq == nullptr) {
     rc = launch_sumsq(a, grad_dtype, *ts, ts->sumsq_local, s);
@@ -237,6 +238,34 @@ int accel_apply_adam(accel_ctx *ctx, int task, float *var, float *m, float *v,
                      const accel_hparams *hp, const float *grad_sumsq_dev, accel_stream_t stream) {
   return apply_common(ctx, task, ACCEL_OPT_ADAM, var, m, v, grads, n_workers, grad_dtype, count,
                       hp, grad_sumsq_dev, stream);
+}
+
+int accel_opt_state_init(void *dev_state, const accel_hparams *hp, uint64_t global_step,
+                         accel_stream_t stream) {
+  if (!dev_state || !hp) return fail(ACCEL_ERR_INVALID, "dev_state/hparams is NULL");
+  if (reinterpret_cast<uintptr_t>(dev_state) & 15)
+    return fail(ACCEL_ERR_ALIGN, "dev_state must be 16-byte aligned");
+  return launch_opt_init(dev_state, hp->beta1_power, hp->beta2_power, global_step,
+                         static_cast<cudaStream_t>(stream));
+}
+
+int accel_apply_dev_state(accel_ctx *ctx, int task, int optimizer, float *var, float *slot0,
+                          float *slot1, const void *const *grads, int n_workers, int grad_dtype,
+                          uint64_t count, const accel_hparams *hp, const float *grad_sumsq_dev,
+                          void *dev_state, accel_stream_t stream) {
+  if (optimizer < ACCEL_OPT_SGD || optimizer > ACCEL_OPT_ADAM)
+    return fail(ACCEL_ERR_INVALID, "unknown optimizer %d", optimizer);
+  if (!dev_state) return fail(ACCEL_ERR_INVALID, "dev_state is NULL");
+  if (reinterpret_cast<uintptr_t>(dev_state) & 15)
+    return fail(ACCEL_ERR_ALIGN, "dev_state must be 16-byte aligned");
+  if (!hp) return fail(ACCEL_ERR_INVALID, "hparams is NULL");
+  int rc = apply_common(ctx, task, optimizer, var, optimizer >= ACCEL_OPT_MOMENTUM ? slot0 : nullptr,
+                        optimizer == ACCEL_OPT_ADAM ? slot1 : nullptr, grads, n_workers,
+                        grad_dtype, count, hp, grad_sumsq_dev, stream,
+                        static_cast<const float *>(dev_state));
+  if (rc) return rc;
+  return launch_opt_advance(dev_state, hp->beta1, hp->beta2, optimizer == ACCEL_OPT_ADAM,
+                            static_cast<cudaStream_t>(stream));
 }
 
 int accel_adam_advance(accel_hparams *hp) {

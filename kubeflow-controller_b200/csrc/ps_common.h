@@ -72,6 +72,7 @@ struct ApplyArgs {
   float *slot1;
   const void *grad[ACCEL_MAX_WORKERS];
   const float *sumsq;  // device scalar for clipping, or nullptr
+  const float *dev_powers;  // device {beta1_power, beta2_power} (Adam), or nullptr: use `alpha`
   uint64_t count;
   int n_workers;
   int use_nesterov;
@@ -94,5 +95,8 @@ int launch_apply(int optimizer, int grad_dtype, const ApplyArgs &a, const TaskSt
                  const Tuning &tune, cudaStream_t stream);
 int launch_sumsq(const ApplyArgs &a, int grad_dtype, const TaskState &ts, float *out,
                  cudaStream_t stream);
+int launch_opt_advance(void *dev_state, float beta1, float beta2, int is_adam, cudaStream_t stream);
+int launch_opt_init(void *dev_state, float beta1_power, float beta2_power, uint64_t global_step,
+                    cudaStream_t stream);
 
 }  // namespace accel

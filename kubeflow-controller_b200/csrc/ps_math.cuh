@@ -39,6 +39,12 @@ __device__ __forceinline__ Scalars make_scalars(const ApplyArgs &a) {
   s.omb1 = a.one_minus_beta1;
   s.omb2 = a.one_minus_beta2;
   s.alpha = a.alpha;
+  if (a.dev_powers != nullptr) {
+    // beta powers live on the device: alpha = lr * sqrt(1 - beta2^t) / (1 - beta1^t), the same
+    // fp32 operations in the same order as the host computes it
+    const float b1p = __ldg(a.dev_powers), b2p = __ldg(a.dev_powers + 1);
+    s.alpha = __fdiv_rn(__fmul_rn(a.lr, __fsqrt_rn(__fsub_rn(1.0f, b2p))), __fsub_rn(1.0f, b1p));
+  }
   s.eps = a.epsilon;
   s.mean_div = a.mean_div;
   s.nesterov = a.use_nesterov != 0;

@@ -135,6 +135,40 @@ int launch_sumsq(const ApplyArgs &a, int grad_dtype, const TaskState &ts, float 
 
 }  // namespace accel
 
+// ---- optimizer state that advances on the device ------------------------------------------
+// Layout of the 16-byte device block: float beta1_power, float beta2_power, uint64 global_step.
+namespace accel {
+
+__global__ void ps_opt_init(float *state, float b1p, float b2p, unsigned long long step) {
+  state[0] = b1p;
+  state[1] = b2p;
+  *reinterpret_cast<unsigned long long *>(state + 2) = step;
+}
+
+// TF-1.4 AdamOptimizer._finish: beta_power *= beta (fp32); global_step += 1 per apply.
+__global__ void ps_opt_advance(float *state, float beta1, float beta2, int is_adam) {
+  if (is_adam) {
+    state[0] = __fmul_rn(state[0], beta1);
+    state[1] = __fmul_rn(state[1], beta2);
+  }
+  *reinterpret_cast<unsigned long long *>(state + 2) += 1ull;
+}
+
+int launch_opt_init(void *dev_state, float b1p, float b2p, uint64_t step, cudaStream_t stream) {
+  ps_opt_init<<<1, 1, 0, stream>>>(static_cast<float *>(dev_state), b1p, b2p, step);
+  ACCEL_CUDA(cudaGetLastError());
+  return ACCEL_OK;
+}
+
+int launch_opt_advance(void *dev_state, float beta1, float beta2, int is_adam,
+                       cudaStream_t stream) {
+  ps_opt_advance<<<1, 1, 0, stream>>>(static_cast<float *>(dev_state), beta1, beta2, is_adam);
+  ACCEL_CUDA(cudaGetLastError());
+  return ACCEL_OK;
+}
+
+}  // namespace accel
+
 // ---- the entry point that allocates nothing -----------------------------------------
 //
 // Same kernel, but its scratch (CTA partials + the ticket word) is this file-scope

@@ -101,6 +101,7 @@ __global__ void __launch_bounds__(512) ps_apply_pull(const __grid_constant__ Sha
 
   ApplyArgs sa;  // scalars only; make_scalars reads nothing else
   sa.sumsq = a.sumsq;
+  sa.dev_powers = nullptr;
   sa.use_nesterov = a.use_nesterov;
   sa.lr = a.lr;
   sa.momentum = a.momentum;

@@ -144,6 +144,7 @@ __global__ void __launch_bounds__(kFusedThreads, 2)
 
   ApplyArgs sa;  // scalars only
   sa.sumsq = a.sumsq;
+  sa.dev_powers = nullptr;
   sa.use_nesterov = a.use_nesterov;
   sa.lr = a.lr;
   sa.momentum = a.momentum;

@@ -19,7 +19,7 @@ from . import accel, placement
 class ParameterServer:
     def __init__(self, argv=None, *, task_index=None, n_ps=None, var_elems, optimizer,
                  hparams: accel.HParams, sharding="round_robin", first_task=0, align_elems=64,
-                 ctx: accel.Context | None = None, gpu_ordinals=None):
+                 ctx: accel.Context | None = None, gpu_ordinals=None, device_state=False):
         if argv is not None:
             job, task_index, _, n_ps = placement.parse_argv(list(argv))
             if job != "ps":
@@ -52,6 +52,16 @@ class ParameterServer:
         self.slot1 = torch.zeros(n, dtype=torch.float32, device=self.device) \
             if optimizer == accel.OPT_ADAM else None
 
+        # optional: Adam's beta powers and the global step live on the GPU and advance there, so a
+        # step has no host-side mutable input (it can be recorded once and replayed)
+        self.dev_state = None
+        if device_state:
+            self.dev_state = torch.zeros(4, dtype=torch.float32, device=self.device)
+            self.ctx.opt_state_init(self.dev_state, self.hp, 0)
+
+    def device_global_step(self) -> int:
+        return int(self.dev_state[2:4].view(torch.int64).item())
+
     def variable(self, k: int) -> torch.Tensor:
         """View of variable k (creation index) inside this task's arena."""
         for kk, off, n in self.layout or ():
@@ -62,6 +72,12 @@ class ParameterServer:
     def apply_gradients(self, worker_grads, stream=None) -> None:
         """One step: worker_grads[w] is worker w's gradient for this task's arena
         (device tensor of `count` elements, fp32 or bf16)."""
+        if self.dev_state is not None:
+            self.ctx.apply_dev_state(self.optimizer, self.var, self.slot0, self.slot1,
+                                     worker_grads, self.hp, self.dev_state, task=self.task,
+                                     count=self.count, stream=stream)
+            self.global_step += 1          # the authoritative counter is the device one
+            return
         if self.count:
             self.ctx.apply(self.optimizer, self.var, self.slot0, self.slot1, worker_grads,
                            self.hp, task=self.task, count=self.count, stream=stream)
@@ -89,6 +105,10 @@ class ParameterServer:
 
         import numpy as np
         os.makedirs(model_dir, exist_ok=True)
+        if self.dev_state is not None:     # the device holds the authoritative powers and step
+            b = self.dev_state[:2].cpu()
+            self.hp.beta1_power, self.hp.beta2_power = float(b[0]), float(b[1])
+            self.global_step = self.device_global_step()
         path = os.path.join(model_dir, f"ps-{self.task}-of-{self.n_ps}.npz")
         hp = {name: getattr(self.hp, name) for name, _ in self.hp._fields_}
         arrays = {"var": self.var.cpu().numpy(), "global_step": np.int64(self.global_step),
@@ -124,6 +144,8 @@ class ParameterServer:
             is_float = fields[str(name)] is ctypes.c_float
             setattr(self.hp, str(name), float(value) if is_float else int(value))
         self.global_step = int(z["global_step"])
+        if self.dev_state is not None:
+            self.ctx.opt_state_init(self.dev_state, self.hp, self.global_step)
 
     def _finish(self) -> None:
         if self.optimizer == accel.OPT_ADAM:

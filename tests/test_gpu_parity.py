@@ -339,12 +339,14 @@ def test_async_mode_applies_each_push_alone(pkg):
     assert np.array_equal(ps.pull().cpu().numpy(), var)
 
 
-def test_checkpoint_restore_resumes_bit_exact(pkg, tmp_path):
+@pytest.mark.parametrize("device_state", [False, True])
+def test_checkpoint_restore_resumes_bit_exact(pkg, tmp_path, device_state):
     sizes = [1000, 24, 4096]
 
     def make():
         return pkg.ParameterServer(task_index=0, n_ps=1, var_elems=sizes, optimizer=pkg.OPT_ADAM,
-                                   hparams=pkg.HParams(lr=0.01), align_elems=8)
+                                   hparams=pkg.HParams(lr=0.01), align_elems=8,
+                                   device_state=device_state)
     rng = np.random.default_rng(1)
     a = make()
     a.var.copy_(torch.from_numpy(rng.standard_normal(a.count).astype(F)))
@@ -361,7 +363,10 @@ def test_checkpoint_restore_resumes_bit_exact(pkg, tmp_path):
     for g in grads[3:]:
         b.apply_gradients(g)
     assert torch.equal(a.var, b.var) and torch.equal(a.slot0, b.slot0) and torch.equal(a.slot1, b.slot1)
-    assert a.hp.beta2_power == b.hp.beta2_power and b.global_step == 6
+    if device_state:
+        assert torch.equal(a.dev_state, b.dev_state) and b.device_global_step() == 6
+    else:
+        assert a.hp.beta2_power == b.hp.beta2_power and b.global_step == 6
 
 
 def test_host_step_with_registered_numpy_buffers(pkg, ctx):
@@ -383,3 +388,63 @@ def test_host_step_with_registered_numpy_buffers(pkg, ctx):
     finally:
         for a in grads + [out]:
             pkg.accel.host_unregister(a)
+
+
+# ---- optimizer state that advances on the device ------------------------
+@pytest.mark.parametrize("opt", [O.SGD, O.MOMENTUM, O.ADAM])
+def test_device_resident_optimizer_state(pkg, opt):
+    sizes = [5000, 3, 70_000]
+    ps = pkg.ParameterServer(task_index=0, n_ps=1, var_elems=sizes, optimizer=opt,
+                             hparams=pkg.HParams(lr=0.01, momentum=0.9), align_elems=8,
+                             device_state=True)
+    rng = np.random.default_rng(2)
+    var = rng.standard_normal(ps.count).astype(F)
+    ps.var.copy_(torch.from_numpy(var))
+    s0, s1 = np.zeros(ps.count, F), np.zeros(ps.count, F)
+    ohp = O.HParams(lr=0.01, momentum=0.9)
+    for step in range(25):
+        g = [(0.01 * rng.standard_normal(ps.count)).astype(F) for _ in range(2)]
+        ps.apply_gradients([torch.from_numpy(x).to(DEV) for x in g])
+        O.numpy_ps_step(opt, var, s0, s1, g, ohp)
+        ohp.advance()
+    assert np.array_equal(ps.pull().cpu().numpy(), var)
+    assert ps.device_global_step() == 25
+    if opt == O.ADAM:
+        b = ps.dev_state[:2].cpu().numpy()
+        assert b[0] == F(ohp.beta1_power) and b[1] == F(ohp.beta2_power)
+
+
+def test_recorded_step_replays_correctly(pkg):
+    """With the optimizer state on the device a whole Adam step (apply + finish) is a fixed
+    sequence of launches: record it once in a CUDA graph, replay it with new gradients."""
+    n, workers = 200_000, 4
+    ps = pkg.ParameterServer(task_index=0, n_ps=1, var_elems=[n], optimizer=pkg.OPT_ADAM,
+                             hparams=pkg.HParams(lr=0.01), align_elems=8, device_state=True)
+    rng = np.random.default_rng(3)
+    var = rng.standard_normal(n).astype(F)
+    ps.var.copy_(torch.from_numpy(var))
+    m, v = np.zeros(n, F), np.zeros(n, F)
+    ohp = O.HParams(lr=0.01)
+    static_g = [torch.zeros(ps.count, device=DEV) for _ in range(workers)]
+
+    def next_grads():
+        g = [(0.01 * rng.standard_normal(n)).astype(F) for _ in range(workers)]
+        for dst, src in zip(static_g, g):
+            dst[:n].copy_(torch.from_numpy(src))
+        O.numpy_ps_step(O.ADAM, var, m, v, g, ohp)
+        ohp.advance()
+
+    next_grads()
+    ps.apply_gradients(static_g)                 # first call outside the recording: set-up
+    torch.cuda.synchronize()
+    graph = torch.cuda.CUDAGraph()
+    next_grads()
+    with torch.cuda.graph(graph):
+        ps.apply_gradients(static_g, stream=torch.cuda.current_stream())
+    graph.replay()                               # capture does not execute: this is step 2
+    for _ in range(6):
+        next_grads()
+        graph.replay()
+    torch.cuda.synchronize()
+    assert np.array_equal(ps.var[:n].cpu().numpy(), var)
+    assert ps.device_global_step() == 8
