@@ -282,7 +282,7 @@ def run_sharded(args):
     dist.init_process_group("nccl", device_id=dev)
     sps = ShardedPS(rank, world, local, ELEMS, pkg.OPT_SGD, pkg.HParams(lr=LR), mode=args.mode,
                     n_chunks=args.chunks or None, rendezvous=args.rendezvous,
-                    multicast=args.multicast, pull_dtype=args.pull)
+                    multicast=args.multicast, pull_dtype=args.pull, overlap=None if args.overlap < 0 else args.overlap)
     gen = torch.Generator(device=dev)
     gen.manual_seed(42)
     sps.var.copy_(torch.randn(sps.padded, device=dev, generator=gen))
@@ -361,7 +361,7 @@ def run_sharded(args):
             "vs_baseline": None, "dtype": "f32", "data": "synthetic",
             "config": dict(workload_config(world), mode=sps.mode, chunks=sps.n_chunks,
                            rendezvous=args.rendezvous, multicast=bool(sps.multicast_ptr),
-                           pull=args.pull),
+                           pull=args.pull, overlap=["inline", "roles"][sps.overlap]),
             "steps_per_s": round(1e3 / ms, 2),
             "roofline": {"bound": "hbm", "achieved": round(hbm_bytes / (ms * 1e-3) / 1e9, 2),
                          "peak": peak, "unit": "GB/s",
@@ -399,6 +399,9 @@ def main():
     ap.add_argument("--chunks", type=int, default=0,
                     help="pipeline slices of the sharded step (0 = the harness default per world)")
     ap.add_argument("--rendezvous", default="ipc", choices=["ipc", "symm"])
+    ap.add_argument("--overlap", type=int, default=-1, choices=[-1, 0, 1],
+                    help="one-kernel step: 0 = every CTA pushes then applies, 1 = split roles, "
+                         "-1 = the harness default per world")
     ap.add_argument("--pull", default="f32", choices=["f32", "bf16"],
                     help="dtype of the replicas the pull writes (bf16 halves the pull bytes)")
     ap.add_argument("--multicast", action="store_true",

@@ -448,17 +448,22 @@ int accel_shard_step(accel_ctx *ctx, const accel_peers *peers, int optimizer, fl
                      int n_contrib, const accel_hparams *hp, const float *grad_sumsq_dev,
                      int n_chunks, accel_stream_t stream);
 
+/* How the one-kernel step overlaps its phases.
+ * INLINE: every CTA pushes slice k, then applies whichever earlier slices have
+ *         arrived from all ranks, and blocks only once its own pushes are issued.
+ * ROLES : even CTAs only push (per-warp slice tickets, no CTA barrier), odd CTAs
+ *         only apply + pull, trailing the pushers by one slice. */
+typedef enum accel_overlap { ACCEL_OVERLAP_INLINE = 0, ACCEL_OVERLAP_ROLES = 1 } accel_overlap;
+
 /* The whole step as ONE cooperative kernel per GPU: push, apply, pull and the
- * closing wait overlapped slice by slice inside the kernel (every CTA pushes
- * slice k, then applies whichever earlier slices have arrived from all ranks,
- * and only blocks once its own pushes are issued). Same results as
+ * closing wait overlapped slice by slice inside the kernel. Same results as
  * accel_shard_step, bit for bit. n_slices in [1,64]. Needs all CTAs resident:
  * the launch is cooperative and fails rather than deadlocks if the GPU cannot
  * hold the grid. */
 int accel_shard_step_fused(accel_ctx *ctx, const accel_peers *peers, int optimizer, float *slot0,
                            float *slot1, const void *const *grads, int n_workers, int grad_dtype,
                            int n_contrib, const accel_hparams *hp, const float *grad_sumsq_dev,
-                           int n_slices, accel_stream_t stream);
+                           int n_slices, int overlap, accel_stream_t stream);
 
 /* Development / CI vehicle for the one-kernel step: all n_ranks (<= 8) ranks of a
  * group whose buffers live on ONE GPU are played by one cooperative launch (CTA
@@ -470,7 +475,7 @@ int accel_shard_step_local_group(accel_ctx *ctx, const accel_peers *const *peers
                                  float *const *slot1, const void *const *const *grads,
                                  int n_workers, int grad_dtype, int n_contrib,
                                  const accel_hparams *hp, const float *grad_sumsq_dev,
-                                 int n_slices, accel_stream_t stream);
+                                 int n_slices, int overlap, accel_stream_t stream);
 
 /* Synchronise the stream and report whether any cross-GPU wait of this rank
  * timed out (every device-side wait is bounded; a rank that never arrives turns

@@ -18,6 +18,7 @@ F32, BF16 = 0, 1
 AGG_SUM, AGG_MEAN = 0, 1
 OPT_SGD, OPT_MOMENTUM, OPT_ADAM = 0, 1, 2
 KERNEL_AUTO, KERNEL_LDG128, KERNEL_LDG256, KERNEL_TMA = 0, 1, 2, 3
+OVERLAP_INLINE, OVERLAP_ROLES = 0, 1
 REPLICA_PS, REPLICA_WORKER, REPLICA_LOCAL = 0, 1, 2
 MAX_WORKERS, MAX_PS = 64, 16
 ACTION_NAMES = ["ShouldAddPS", "ShouldAddPSService", "ShouldAddWorker",
@@ -147,10 +148,11 @@ def load_library() -> ctypes.CDLL:
     L.accel_tfjob_is_local_job.argtypes = [ctypes.POINTER(i32), i32]
     L.accel_shard_step.argtypes = [vp, ctypes.POINTER(Peers), i32, vp, vp, pvp, i32, i32, i32, php,
                                    vp, i32, vp]
-    L.accel_shard_step_fused.argtypes = L.accel_shard_step.argtypes
+    L.accel_shard_step_fused.argtypes = [vp, ctypes.POINTER(Peers), i32, vp, vp, pvp, i32, i32, i32,
+                                         php, vp, i32, i32, vp]
     L.accel_shard_step_local_group.argtypes = [vp, ctypes.POINTER(ctypes.POINTER(Peers)), i32, i32,
                                                pvp, pvp, ctypes.POINTER(pvp), i32, i32, i32, php,
-                                               vp, i32, vp]
+                                               vp, i32, i32, vp]
     L.accel_shard_check.argtypes = [vp, ctypes.POINTER(Peers), vp]
     L.accel_dev_alloc.argtypes = [ctypes.c_size_t, pvp]
     L.accel_dev_free.argtypes = [vp]

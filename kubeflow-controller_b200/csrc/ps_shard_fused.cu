@@ -33,6 +33,7 @@ struct FusedArgs {
   ShardArgs r[R];
   int ctas_per_rank;
   int n_slices;
+  int roles;  // ACCEL_OVERLAP_ROLES: even CTAs only push, odd CTAs only apply+pull
   uint32_t epoch_base;  // slice k is published as epoch_base + k + 1, the pull as epoch_base + n_slices
 };
 
@@ -166,31 +167,65 @@ __global__ void __launch_bounds__(kFusedThreads, 2)
     return f + per <= shard_items ? per : shard_items - f;
   };
 
-  int next_apply = 0;
-  for (int k = 0; k < S; ++k) {
-    push_slice<G, NW>(a, slice_first(k), slice_items(k), bid, nb);
-    // per-slice ticket: the last CTA of this rank publishes slice k to every rank
-    __syncthreads();
-    if (threadIdx.x == 0) {
-      __threadfence_system();
-      const unsigned int done = atomicAdd(flags + kFlagSliceTicket + k, 1u);
-      if (done == static_cast<unsigned int>(nb) - 1) {
-        flags[kFlagSliceTicket + k] = 0;
-        __threadfence_system();
-        for (int p = 0; p < a.world; ++p)
-          st_relaxed_sys(a.flags[p] + kFlagPush + a.rank, fa.epoch_base + k + 1);
+  if (fa.roles && nb > 1) {
+    // ---- split roles: pushers never stop to apply, appliers trail them by one slice --------
+    const int n_push = (nb + 1) / 2, n_apply = nb / 2;
+    const int rb = bid >> 1;
+    if ((bid & 1) == 0) {
+      // Pusher. The per-slice ticket is taken per WARP (no CTA barrier): a warp that has
+      // finished its part of slice k fences its own stores and moves on to slice k+1 while the
+      // other warps keep the memory system busy.
+      const unsigned int total_warps = static_cast<unsigned int>(n_push) * (blockDim.x >> 5);
+      for (int k = 0; k < S; ++k) {
+        push_slice<G, NW>(a, slice_first(k), slice_items(k), rb, n_push);
+        __syncwarp();
+        if ((threadIdx.x & 31) == 0) {
+          __threadfence_system();
+          const unsigned int done = atomicAdd(flags + kFlagSliceTicket + k, 1u);
+          if (done == total_warps - 1) {
+            flags[kFlagSliceTicket + k] = 0;
+            __threadfence_system();
+            for (int p = 0; p < a.world; ++p)
+              st_relaxed_sys(a.flags[p] + kFlagPush + a.rank, fa.epoch_base + k + 1);
+          }
+        }
+      }
+    } else {
+      // Applier: blocks (bounded) only on OTHER CTAs' pushes, which never block.
+      for (int k = 0; k < S; ++k) {
+        if (!wait_all(flags, kFlagPush, a.world, fa.epoch_base + k + 1)) return;
+        apply_slice<OPT>(a, sc, slice_first(k), slice_items(k), rb, n_apply);
       }
     }
-    // whatever has already arrived from everybody gets applied now, without waiting
-    while (next_apply < k && poll_all(flags, kFlagPush, a.world, fa.epoch_base + next_apply + 1)) {
-      apply_slice<OPT>(a, sc, slice_first(next_apply), slice_items(next_apply), bid, nb);
-      ++next_apply;
+  } else {
+    // ---- every CTA does both: push slice k, then apply whatever has already arrived --------
+    int next_apply = 0;
+    for (int k = 0; k < S; ++k) {
+      push_slice<G, NW>(a, slice_first(k), slice_items(k), bid, nb);
+      // per-slice ticket: the last CTA of this rank publishes slice k to every rank
+      __syncthreads();
+      if (threadIdx.x == 0) {
+        __threadfence_system();
+        const unsigned int done = atomicAdd(flags + kFlagSliceTicket + k, 1u);
+        if (done == static_cast<unsigned int>(nb) - 1) {
+          flags[kFlagSliceTicket + k] = 0;
+          __threadfence_system();
+          for (int p = 0; p < a.world; ++p)
+            st_relaxed_sys(a.flags[p] + kFlagPush + a.rank, fa.epoch_base + k + 1);
+        }
+      }
+      // whatever has already arrived from everybody gets applied now, without waiting
+      while (next_apply < k &&
+             poll_all(flags, kFlagPush, a.world, fa.epoch_base + next_apply + 1)) {
+        apply_slice<OPT>(a, sc, slice_first(next_apply), slice_items(next_apply), bid, nb);
+        ++next_apply;
+      }
     }
-  }
-  // all pushes of this CTA are issued: now it may block for what is still missing
-  for (; next_apply < S; ++next_apply) {
-    if (!wait_all(flags, kFlagPush, a.world, fa.epoch_base + next_apply + 1)) return;
-    apply_slice<OPT>(a, sc, slice_first(next_apply), slice_items(next_apply), bid, nb);
+    // all pushes of this CTA are issued: now it may block for what is still missing
+    for (; next_apply < S; ++next_apply) {
+      if (!wait_all(flags, kFlagPush, a.world, fa.epoch_base + next_apply + 1)) return;
+      apply_slice<OPT>(a, sc, slice_first(next_apply), slice_items(next_apply), bid, nb);
+    }
   }
   // pull signal, then the closing wait by the CTA that took the last ticket
   __syncthreads();
@@ -286,8 +321,10 @@ extern "C" {
 int accel_shard_step_fused(accel_ctx *ctx, const accel_peers *peers, int optimizer, float *slot0,
                            float *slot1, const void *const *grads, int n_workers, int grad_dtype,
                            int n_contrib, const accel_hparams *hp, const float *grad_sumsq_dev,
-                           int n_slices, accel_stream_t stream) {
+                           int n_slices, int overlap, accel_stream_t stream) {
   if (!peers) return fail(ACCEL_ERR_INVALID, "peers is NULL");
+  if (overlap != ACCEL_OVERLAP_INLINE && overlap != ACCEL_OVERLAP_ROLES)
+    return fail(ACCEL_ERR_INVALID, "unknown overlap %d", overlap);
   TaskState *ts = nullptr;
   int rc = task_state(ctx, peers->rank, &ts);
   if (rc) return rc;
@@ -296,6 +333,7 @@ int accel_shard_step_fused(accel_ctx *ctx, const accel_peers *peers, int optimiz
                  grad_sumsq_dev, &fa.r[0]);
   if (rc) return rc;
   fa.n_slices = clamp_slices(n_slices, peers->shard_elems);
+  fa.roles = overlap == ACCEL_OVERLAP_ROLES;
   fa.epoch_base = ts->shard_epoch;
   ts->shard_epoch += fa.n_slices;
   fa.ctas_per_rank = 0;
@@ -307,7 +345,9 @@ int accel_shard_step_local_group(accel_ctx *ctx, const accel_peers *const *peers
                                  float *const *slot1, const void *const *const *grads,
                                  int n_workers, int grad_dtype, int n_contrib,
                                  const accel_hparams *hp, const float *grad_sumsq_dev,
-                                 int n_slices, accel_stream_t stream) {
+                                 int n_slices, int overlap, accel_stream_t stream) {
+  if (overlap != ACCEL_OVERLAP_INLINE && overlap != ACCEL_OVERLAP_ROLES)
+    return fail(ACCEL_ERR_INVALID, "unknown overlap %d", overlap);
   if (!peers_of_rank || !grads) return fail(ACCEL_ERR_INVALID, "peers_of_rank/grads is NULL");
   if (n_ranks < 1 || n_ranks > kEmuRanks)
     return fail(ACCEL_ERR_INVALID, "n_ranks %d out of range [1,%d]", n_ranks, kEmuRanks);
@@ -332,6 +372,7 @@ int accel_shard_step_local_group(accel_ctx *ctx, const accel_peers *const *peers
     if (rc) return rc;
   }
   fa.n_slices = clamp_slices(n_slices, peers_of_rank[0]->shard_elems);
+  fa.roles = overlap == ACCEL_OVERLAP_ROLES;
   fa.epoch_base = ts0->shard_epoch;
   for (int r = 0; r < n_ranks; ++r) ctx->task[r].shard_epoch += fa.n_slices;
   return launch_fused<kEmuRanks>(fa, n_ranks, optimizer, grad_dtype, *ts0, 2,

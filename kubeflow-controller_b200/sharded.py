@@ -119,7 +119,8 @@ class ShardedPS:
     def __init__(self, rank: int, world: int, device_index: int, elems: int, optimizer: int,
                  hp: accel.HParams, mode: str = "fused", ctx: accel.Context | None = None,
                  peer_ptrs=None, gpu_ordinals=None, n_chunks: int | None = None,
-                 rendezvous: str = "ipc", multicast: bool = False, pull_dtype: str = "f32"):
+                 rendezvous: str = "ipc", multicast: bool = False, pull_dtype: str = "f32",
+                 overlap: int | None = None):
         if mode not in ("fused", "streams", "nccl"):
             raise ValueError(f"unknown mode {mode!r}")
         if rendezvous not in ("ipc", "symm"):
@@ -133,6 +134,9 @@ class ShardedPS:
         # slices of the step: measured on B200, overlap pays at 2 ranks (4 slices: 0.817 ms vs
         # 0.874 ms) and costs at 8 (1 slice: 1.166 ms, 2: 1.184 ms, 4: 1.299 ms)
         self.n_chunks = n_chunks or (4 if world <= 2 else 2 if world <= 4 else 1)
+        # split roles measured faster at 2 ranks (0.773 vs 0.815 ms) and slower at 4 (1.012 vs 0.983)
+        self.overlap = overlap if overlap is not None else \
+            (accel.OVERLAP_ROLES if world <= 2 else accel.OVERLAP_INLINE)
         self.multicast_ptr = 0
         self.device_index = device_index
         self.device = torch.device("cuda", device_index)
@@ -275,13 +279,15 @@ class ShardedPS:
             self.apply_pull(n_contrib, ss, stream, epoch=epoch)
             self.wait_pull(stream, epoch)
         elif self.mode in ("fused", "streams"):
-            fn = self.lib.accel_shard_step_fused if self.mode == "fused" \
-                else self.lib.accel_shard_step
-            accel.check(fn(
-                self.ctx.handle, ctypes.byref(self.peers), self.optimizer,
-                accel._ptr(self.slot0), accel._ptr(self.slot1), accel._grad_array(grads),
-                len(grads), accel._grad_dtype(grads[0]), n_contrib, ctypes.byref(self.hp),
-                accel._ptr(sumsq), self.n_chunks, accel._stream_handle(stream)))
+            head = (self.ctx.handle, ctypes.byref(self.peers), self.optimizer,
+                    accel._ptr(self.slot0), accel._ptr(self.slot1), accel._grad_array(grads),
+                    len(grads), accel._grad_dtype(grads[0]), n_contrib, ctypes.byref(self.hp),
+                    accel._ptr(sumsq), self.n_chunks)
+            if self.mode == "fused":      # one cooperative kernel
+                accel.check(self.lib.accel_shard_step_fused(*head, self.overlap,
+                                                            accel._stream_handle(stream)))
+            else:                         # separate kernels, slices pipelined over two streams
+                accel.check(self.lib.accel_shard_step(*head, accel._stream_handle(stream)))
         else:
             import torch.distributed as dist
             if self.hp.aggregate != accel.AGG_SUM:
@@ -331,7 +337,8 @@ def local_group_step(ranks, grads_per_rank, stream=None, sumsq=None):
         x.finish_step()
 
 
-def local_group_step_fused(ranks, grads_per_rank, n_slices=None, stream=None, sumsq=None):
+def local_group_step_fused(ranks, grads_per_rank, n_slices=None, stream=None, sumsq=None,
+                           overlap=accel.OVERLAP_INLINE):
     """One step of the emulated group through the ONE-kernel path: a single cooperative
     launch plays every rank (accel_shard_step_local_group)."""
     n = len(ranks)
@@ -347,7 +354,7 @@ def local_group_step_fused(ranks, grads_per_rank, n_slices=None, stream=None, su
     accel.check(x0.lib.accel_shard_step_local_group(
         x0.ctx.handle, peers, n, x0.optimizer, s0, s1, gg, len(grads_per_rank[0]),
         accel._grad_dtype(grads_per_rank[0][0]), n_contrib, ctypes.byref(x0.hp),
-        accel._ptr(sumsq), n_slices or x0.n_chunks, accel._stream_handle(stream)))
+        accel._ptr(sumsq), n_slices or x0.n_chunks, overlap, accel._stream_handle(stream)))
     for x in ranks:
         x.check(stream)
         x.finish_step()

@@ -143,7 +143,8 @@ def test_single_rank_pipelined_step_call(pkg):
 @pytest.mark.parametrize("world,slices", [(1, 1), (2, 1), (2, 4), (4, 7), (8, 16), (8, 64)])
 @pytest.mark.parametrize("opt", [O.SGD, O.MOMENTUM, O.ADAM])
 @pytest.mark.parametrize("workers,bf16,mean", [(1, False, False), (8, False, True), (5, True, True)])
-def test_one_kernel_step_matches_oracle(pkg, world, slices, opt, workers, bf16, mean):
+@pytest.mark.parametrize("overlap", [0, 1])
+def test_one_kernel_step_matches_oracle(pkg, world, slices, opt, workers, bf16, mean, overlap):
     """The ONE-kernel step (push, apply, pull and closing wait overlapped inside a cooperative
     launch), all ranks played by one launch on this GPU: bit-exact against the oracle."""
     from kubeflow_controller_b200 import sharded
@@ -166,7 +167,7 @@ def test_one_kernel_step_matches_oracle(pkg, world, slices, opt, workers, bf16, 
                 g = [O.f32_to_bf16_bits(x) for x in g]
             gpr.append(g)
         sharded.local_group_step_fused(ranks, [[_dev(g) for g in gr] for gr in gpr],
-                                       n_slices=slices)
+                                       n_slices=slices, overlap=overlap)
         O.numpy_apply(opt, var, s0, s1, _oracle_hier(gpr, mean), ohp)
         ohp.advance()
     torch.cuda.synchronize()

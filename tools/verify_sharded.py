@@ -26,12 +26,13 @@ def main():
     dist.init_process_group("nccl", device_id=dev)
     elems, workers, steps = 400_003, 3, 3
     ok = True
-    variants = [("fused", "ipc", 1), ("fused", "ipc", 16), ("fused", "symm", 8),
-                ("streams", "ipc", 4), ("nccl", "ipc", 1)]
+    variants = [("fused", "ipc", 1), ("fused", "ipc", 16), ("fused-roles", "ipc", 8),
+                ("fused", "symm", 8), ("streams", "ipc", 4), ("nccl", "ipc", 1)]
     for mode, rdv, chunks in variants:
         for opt, bf16 in ((pkg.OPT_SGD, False), (pkg.OPT_ADAM, True), (pkg.OPT_MOMENTUM, False)):
             sps = ShardedPS(rank, world, local, elems, opt, pkg.HParams(lr=0.01, momentum=0.9),
-                            mode=mode, rendezvous=rdv, n_chunks=chunks, multicast=False)
+                            mode=mode.split("-")[0], rendezvous=rdv, n_chunks=chunks,
+                            multicast=False, overlap=int(mode.endswith("roles")))
             padded = sps.padded
             rng = np.random.default_rng(7)          # same stream on every rank
             var = rng.standard_normal(padded).astype(F)
