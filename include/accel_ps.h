@@ -36,7 +36,7 @@
 extern "C" {
 #endif
 
-#define ACCEL_PS_VERSION 10100 /* major*10000 + minor*100 + patch */
+#define ACCEL_PS_VERSION 10200 /* major*10000 + minor*100 + patch */
 #define ACCEL_MAX_WORKERS 64   /* gradients summed by one launch */
 #define ACCEL_MAX_PS 16        /* PS tasks (= GPUs of one box) per context */
 
@@ -197,10 +197,26 @@ int accel_adam_advance(accel_hparams *hp);
  * replayed. slot0/slot1 are ignored where the optimizer has no such slot. */
 int accel_opt_state_init(void *dev_state, const accel_hparams *hp, uint64_t global_step,
                          accel_stream_t stream);
+/* TF's finish step on its own: powers *= betas (when is_adam), global_step += 1.
+ * accel_apply_dev_state runs it after EVERY call — correct when a task's
+ * variables live in one flat arena (one call per step). A task that applies
+ * several variables per step (accel_plan_round_robin buckets applied one by
+ * one) uses accel_apply_dev_state_ex with advance = 0 and calls this once. */
+int accel_opt_state_advance(void *dev_state, const accel_hparams *hp, int is_adam,
+                            accel_stream_t stream);
 int accel_apply_dev_state(accel_ctx *ctx, int task, int optimizer, float *var, float *slot0,
                           float *slot1, const void *const *grads, int n_workers, int grad_dtype,
                           uint64_t count, const accel_hparams *hp, const float *grad_sumsq_dev,
                           void *dev_state, accel_stream_t stream);
+/* accel_apply_dev_state with the finish step under the caller's control:
+ * advance = 0 applies only (call accel_opt_state_advance once after the LAST
+ * variable of the step, as TF-1.4's AdamOptimizer._finish does); advance != 0
+ * is accel_apply_dev_state. */
+int accel_apply_dev_state_ex(accel_ctx *ctx, int task, int optimizer, float *var, float *slot0,
+                             float *slot1, const void *const *grads, int n_workers,
+                             int grad_dtype, uint64_t count, const accel_hparams *hp,
+                             const float *grad_sumsq_dev, void *dev_state, int advance,
+                             accel_stream_t stream);
 
 /* out_sumsq_dev[0] = sum over [0,count) of G^2, G = aggregate(grads), for
  * tf.clip_by_global_norm. Deterministic for a given launch
@@ -385,7 +401,17 @@ int accel_dev_free(void *dev_ptr);
  *               pull delivers the updated variables rounded to bf16 (nearest-even)
  *               into every rank's var_bf16 — half the NVLink bytes — and the fp32
  *               values stay with the owner only (its shard inside var[rank]).
- *               For workers that compute in bf16 (SURVEY §8 f, rank 2). */
+ *               For workers that compute in bf16 (SURVEY §8 f, rank 2).
+ *   stage_multicast : optional NVSwitch multicast mapping covering every rank's
+ *               stage buffer; with var_multicast it enables the in-switch form of
+ *               the step (ACCEL_OVERLAP_SWITCH below). NULL otherwise.
+ *   stage_dtype : ACCEL_F32 (0, the default) — stage slots hold fp32 partial sums.
+ *               ACCEL_BF16 — every rank pushes exactly ONE bf16 gradient
+ *               (n_workers = 1, grad_dtype = ACCEL_BF16; BASELINE config 4), so the
+ *               "partial sum" IS that gradient and travels as raw bf16: half the
+ *               reduce-scatter bytes. The owner widens (exact) and sums in rank
+ *               order in fp32, so results are bit-identical to fp32 slots. All
+ *               ranks of a step must use the same value. */
 #define ACCEL_SHARD_FLAG_WORDS 256
 typedef struct accel_peers {
   int32_t rank;
@@ -396,6 +422,9 @@ typedef struct accel_peers {
   uint32_t *const *flags;
   float *var_multicast;
   uint16_t *const *var_bf16;
+  float *stage_multicast;
+  int32_t stage_dtype;
+  int32_t reserved0;
 } accel_peers;
 
 /* Push (the worker->PS reduce-scatter, fused): sum this rank's n_workers local
@@ -452,8 +481,29 @@ int accel_shard_step(accel_ctx *ctx, const accel_peers *peers, int optimizer, fl
  * INLINE: every CTA pushes slice k, then applies whichever earlier slices have
  *         arrived from all ranks, and blocks only once its own pushes are issued.
  * ROLES : even CTAs only push (per-warp slice tickets, no CTA barrier), odd CTAs
- *         only apply + pull, trailing the pushers by one slice. */
-typedef enum accel_overlap { ACCEL_OVERLAP_INLINE = 0, ACCEL_OVERLAP_ROLES = 1 } accel_overlap;
+ *         only apply + pull, trailing the pushers by one slice.
+ * SWITCH: the in-switch (NVLS) form. Each rank first writes the sum of its local
+ *         gradients for the WHOLE arena into its own stage buffer (layout
+ *         [world*shard], not slots); the owner of shard r then reads
+ *         stage_multicast at its shard with multimem.ld_reduce — the NVSwitch
+ *         fetches the `world` local sums and adds them — applies the optimizer,
+ *         and writes the result through var_multicast with multimem.st, which
+ *         the switch delivers to every replica. Per GPU and direction NVLink
+ *         carries (1 + 1/world) of the arena instead of 2(world-1)/world. A
+ *         few CTAs reduce+apply+pull while the others sum, slice by slice. The
+ *         switch adds in its own order: results match the other forms within
+ *         the path's tolerance (rel 1e-5), not bit for bit; with stage_dtype
+ *         ACCEL_BF16 the switch returns the sum rounded to bf16 (fp32
+ *         accumulation) — within the bf16 path's rel 1e-2. Needs
+ *         stage_multicast and var_multicast. When both are NULL the same
+ *         protocol runs with `world` peer loads summed in rank order and
+ *         `world` peer stores instead (bit-exact; the form a single GPU can run
+ *         under accel_shard_step_local_group). */
+typedef enum accel_overlap {
+  ACCEL_OVERLAP_INLINE = 0,
+  ACCEL_OVERLAP_ROLES = 1,
+  ACCEL_OVERLAP_SWITCH = 2
+} accel_overlap;
 
 /* The whole step as ONE cooperative kernel per GPU: push, apply, pull and the
  * closing wait overlapped slice by slice inside the kernel. Same results as
@@ -481,6 +531,40 @@ int accel_shard_step_local_group(accel_ctx *ctx, const accel_peers *const *peers
  * timed out (every device-side wait is bounded; a rank that never arrives turns
  * into ACCEL_ERR_STATE here instead of a hung GPU). */
 int accel_shard_check(accel_ctx *ctx, const accel_peers *peers, accel_stream_t stream);
+
+/* Recover after accel_shard_check reported a timeout: synchronise the stream,
+ * zero this rank's flag words (tickets, epochs, status) and restart its epoch
+ * counter at 0. EVERY rank of the group must call it, with a host-side barrier
+ * between the last reset and the next step (a peer that still publishes old
+ * epochs into freshly zeroed words would be taken for the new step). No
+ * reference counterpart (TF-1.4 aborts the session on a lost PS). */
+int accel_shard_reset(accel_ctx *ctx, const accel_peers *peers, accel_stream_t stream);
+
+/* Share of the one-kernel step's CTAs that reduce + apply + pull under
+ * ACCEL_OVERLAP_SWITCH (percent, 1..90; 0 restores the default of 25).
+ * coop = 1 (default) launches the one-kernel step cooperatively (co-residency
+ * guaranteed or the launch fails); coop = 0 uses a plain launch when the grid
+ * is at most one CTA per SM — lower launch latency for small shards, safe only
+ * while nothing else occupies the GPU (waits stay bounded either way).
+ * Benchmark/tuning knob; no reference counterpart. */
+int accel_ctx_set_step_shape(accel_ctx *ctx, int reducer_pct, int coop);
+
+/* The sharded step with HOST gradient buffers, per rank (the N > 1 twin of
+ * accel_ps_step_host; replaces the gRPC-into-host-memory arrangement of
+ * examples/workdir/mnist_replica.py:251-264 on every PS pod of the box). The
+ * arena is cut into n_slices slices (the same sub-range of every shard); for
+ * slice k the n_workers pinned host gradients are copied to context-owned
+ * device buffers over this rank's PCIe link while slice k-1 runs
+ * accel_shard_push -> accel_shard_apply_pull on a second stream and slice k-2's
+ * part of the updated replica returns to host_var_out (world*shard fp32; may be
+ * NULL) on a third. Returns when the step is complete on this rank. All ranks
+ * must call it with the same n_slices. Device gradient buffers (n_workers x
+ * arena) are allocated by the context at first use and kept. clip_norm must be
+ * 0 (the global norm needs the whole gradient first). */
+int accel_shard_step_host(accel_ctx *ctx, const accel_peers *peers, int optimizer, float *slot0,
+                          float *slot1, const void *const *host_grads, int n_workers,
+                          int grad_dtype, int n_contrib, const accel_hparams *hp,
+                          float *host_var_out, int n_slices);
 
 #ifdef __cplusplus
 } /* extern "C" */

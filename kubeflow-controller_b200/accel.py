@@ -18,7 +18,7 @@ F32, BF16 = 0, 1
 AGG_SUM, AGG_MEAN = 0, 1
 OPT_SGD, OPT_MOMENTUM, OPT_ADAM = 0, 1, 2
 KERNEL_AUTO, KERNEL_LDG128, KERNEL_LDG256, KERNEL_TMA = 0, 1, 2, 3
-OVERLAP_INLINE, OVERLAP_ROLES = 0, 1
+OVERLAP_INLINE, OVERLAP_ROLES, OVERLAP_SWITCH = 0, 1, 2
 REPLICA_PS, REPLICA_WORKER, REPLICA_LOCAL = 0, 1, 2
 MAX_WORKERS, MAX_PS = 64, 16
 ACTION_NAMES = ["ShouldAddPS", "ShouldAddPSService", "ShouldAddWorker",
@@ -29,14 +29,16 @@ SYMBOLS = [
     "accel_version", "accel_last_error", "accel_ctx_create", "accel_ctx_destroy",
     "accel_ctx_gpu_of", "accel_ctx_set_kernel", "accel_plan_flat", "accel_plan_round_robin",
     "accel_apply_sgd", "accel_apply_momentum", "accel_apply_adam", "accel_adam_advance",
-    "accel_opt_state_init", "accel_apply_dev_state",
+    "accel_opt_state_init", "accel_opt_state_advance", "accel_apply_dev_state",
+    "accel_apply_dev_state_ex",
     "accel_grad_sumsq", "accel_grad_sumsq_static", "accel_ps_step_host", "accel_host_register", "accel_host_unregister",
     "accel_tfjob_action", "accel_tfjob_is_local_job", "accel_tfjob_sync_plan",
     "accel_tfjob_service_key", "accel_tfjob_cluster_spec",
     "accel_tfjob_labels", "accel_tfjob_parse_argv", "accel_ipc_export", "accel_ipc_open",
     "accel_ipc_close", "accel_dev_alloc", "accel_dev_free", "accel_shard_push",
     "accel_shard_apply_pull", "accel_shard_wait_push", "accel_shard_wait_pull", "accel_shard_step", "accel_shard_step_fused",
-    "accel_shard_step_local_group", "accel_shard_check",
+    "accel_shard_step_local_group", "accel_shard_check", "accel_shard_reset",
+    "accel_ctx_set_step_shape", "accel_shard_step_host",
 ]
 
 
@@ -82,7 +84,10 @@ class Peers(ctypes.Structure):
                 ("var", ctypes.POINTER(ctypes.c_void_p)),
                 ("flags", ctypes.POINTER(ctypes.c_void_p)),
                 ("var_multicast", ctypes.c_void_p),
-                ("var_bf16", ctypes.POINTER(ctypes.c_void_p))]
+                ("var_bf16", ctypes.POINTER(ctypes.c_void_p)),
+                ("stage_multicast", ctypes.c_void_p),
+                ("stage_dtype", ctypes.c_int32),
+                ("reserved0", ctypes.c_int32)]
 
 
 _lib = None
@@ -117,6 +122,9 @@ def load_library() -> ctypes.CDLL:
     L.accel_adam_advance.argtypes = [php]
     L.accel_opt_state_init.argtypes = [vp, php, u64, vp]
     L.accel_apply_dev_state.argtypes = [vp, i32, i32, vp, vp, vp, pvp, i32, i32, u64, php, vp, vp, vp]
+    L.accel_apply_dev_state_ex.argtypes = [vp, i32, i32, vp, vp, vp, pvp, i32, i32, u64, php, vp,
+                                           vp, i32, vp]
+    L.accel_opt_state_advance.argtypes = [vp, php, i32, vp]
     L.accel_grad_sumsq.argtypes = [vp, i32, pvp, i32, i32, u64, i32, vp, vp]
     L.accel_grad_sumsq_static.argtypes = [pvp, i32, i32, u64, i32, vp, vp]
     L.accel_ps_step_host.argtypes = [vp, i32, i32, vp, vp, vp, pvp, i32, i32, u64, php, vp]
@@ -154,6 +162,10 @@ def load_library() -> ctypes.CDLL:
                                                pvp, pvp, ctypes.POINTER(pvp), i32, i32, i32, php,
                                                vp, i32, i32, vp]
     L.accel_shard_check.argtypes = [vp, ctypes.POINTER(Peers), vp]
+    L.accel_shard_reset.argtypes = [vp, ctypes.POINTER(Peers), vp]
+    L.accel_ctx_set_step_shape.argtypes = [vp, i32, i32]
+    L.accel_shard_step_host.argtypes = [vp, ctypes.POINTER(Peers), i32, vp, vp, pvp, i32, i32, i32,
+                                        php, vp, i32]
     L.accel_dev_alloc.argtypes = [ctypes.c_size_t, pvp]
     L.accel_dev_free.argtypes = [vp]
     for name in SYMBOLS:
@@ -239,6 +251,9 @@ class Context:
     def set_kernel(self, kernel=KERNEL_AUTO, threads=0, ctas_per_sm=0, unroll=0):
         check(self.lib.accel_ctx_set_kernel(self.handle, kernel, threads, ctas_per_sm, unroll))
 
+    def set_step_shape(self, reducer_pct=0, coop=True):
+        check(self.lib.accel_ctx_set_step_shape(self.handle, reducer_pct, int(bool(coop))))
+
     # ---- the hot path ---------------------------------------------------------
     def apply_sgd(self, var, grads, hp: HParams, task=0, count=None, sumsq=None, stream=None):
         n = var.numel() if count is None else count
@@ -282,6 +297,20 @@ class Context:
                                              _ptr(slot1), _grad_array(grads), len(grads),
                                              _grad_dtype(grads[0]), n, ctypes.byref(hp),
                                              _ptr(sumsq), _ptr(dev_state), _stream_handle(stream)))
+
+    def apply_dev_state_ex(self, optimizer, var, slot0, slot1, grads, hp: HParams, dev_state,
+                           advance: bool, task=0, count=None, sumsq=None, stream=None):
+        """apply_dev_state with the finish step under the caller's control (several variables
+        per step: advance=False on each, then opt_state_advance once)."""
+        n = var.numel() if count is None else count
+        check(self.lib.accel_apply_dev_state_ex(
+            self.handle, task, optimizer, _ptr(var), _ptr(slot0), _ptr(slot1), _grad_array(grads),
+            len(grads), _grad_dtype(grads[0]), n, ctypes.byref(hp), _ptr(sumsq), _ptr(dev_state),
+            int(bool(advance)), _stream_handle(stream)))
+
+    def opt_state_advance(self, dev_state, hp: HParams, is_adam: bool, stream=None):
+        check(self.lib.accel_opt_state_advance(_ptr(dev_state), ctypes.byref(hp),
+                                               int(bool(is_adam)), _stream_handle(stream)))
 
     def grad_sumsq(self, grads, out, aggregate=AGG_SUM, task=0, count=None, stream=None):
         n = grads[0].numel() if count is None else count

@@ -83,7 +83,25 @@ def build(verbose: bool = False, force: bool = False) -> str:
             raise RuntimeError(f"link failed:\n{p.stdout}\n{p.stderr}")
     if verbose:
         sys.stderr.write("\n".join(logs))
+    build_probe()
     return LIB
+
+
+def build_probe() -> str:
+    """tools/probe/libaccel_probe.so: link-rate probes for development, kept OUT of the product
+    library (nothing in the package loads it)."""
+    src = os.path.join(ROOT, "tools", "probe", "ps_probe.cu")
+    out = os.path.join(ROOT, "tools", "probe", "libaccel_probe.so")
+    if not os.path.exists(src):
+        return ""
+    if os.path.exists(out) and os.path.getmtime(out) > os.path.getmtime(src):
+        return out
+    cmd = [nvcc(), "-O3", "-std=c++17", "-lineinfo", *ARCH, "-Xcompiler", "-fPIC", "-shared",
+           "-cudart", "static", "-o", out, src]
+    p = subprocess.run(cmd, capture_output=True, text=True)
+    if p.returncode != 0:
+        raise RuntimeError(f"nvcc failed on {src}:\n{p.stdout}\n{p.stderr}")
+    return out
 
 
 if __name__ == "__main__":

@@ -76,6 +76,11 @@ static void task_release(TaskState &ts) {
   if (ts.shard_aux) cudaStreamDestroy(ts.shard_aux);
   if (ts.shard_ev_push) cudaEventDestroy(ts.shard_ev_push);
   if (ts.shard_ev_done) cudaEventDestroy(ts.shard_ev_done);
+  if (ts.host_step_grads) cudaFree(ts.host_step_grads);
+  for (int i = 0; i < TaskState::kHostSlices; ++i) {
+    if (ts.ev_slice_in[i]) cudaEventDestroy(ts.ev_slice_in[i]);
+    if (ts.ev_slice_done[i]) cudaEventDestroy(ts.ev_slice_done[i]);
+  }
   ts = TaskState();
 }
 
@@ -155,6 +160,35 @@ static int apply_common(accel_ctx *ctx, int task, int optimizer, float *var, flo
     a.sumsq = ts->sumsq_local;
   }
   return launch_apply(optimizer, grad_dtype, a, *ts, ctx->tuning, s);
+}
+
+int ensure_host_streams(TaskState &ts) {
+  if (!ts.copy_in) {
+    ACCEL_CUDA(cudaStreamCreateWithFlags(&ts.copy_in, cudaStreamNonBlocking));
+    ACCEL_CUDA(cudaStreamCreateWithFlags(&ts.compute, cudaStreamNonBlocking));
+    ACCEL_CUDA(cudaStreamCreateWithFlags(&ts.copy_out, cudaStreamNonBlocking));
+    for (int i = 0; i < 2; ++i) {
+      ACCEL_CUDA(cudaEventCreateWithFlags(&ts.ev_in[i], cudaEventDisableTiming));
+      ACCEL_CUDA(cudaEventCreateWithFlags(&ts.ev_free[i], cudaEventDisableTiming));
+      ACCEL_CUDA(cudaEventCreateWithFlags(&ts.ev_done[i], cudaEventDisableTiming));
+    }
+  }
+  return ACCEL_OK;
+}
+
+static int ensure_host_step(TaskState &ts, size_t stage_bytes) {
+  int rc = ensure_host_streams(ts);
+  if (rc) return rc;
+  if (ts.stage_bytes < stage_bytes) {
+    for (int i = 0; i < 2; ++i) {
+      if (ts.stage_buf[i]) ACCEL_CUDA(cudaFree(ts.stage_buf[i]));
+      ts.stage_buf[i] = nullptr;
+    }
+    ts.stage_bytes = 0;
+    for (int i = 0; i < 2; ++i) ACCEL_CUDA(cudaMalloc(&ts.stage_buf[i], stage_bytes));
+    ts.stage_bytes = stage_bytes;
+  }
+  return ACCEL_OK;
 }
 
 }  // namespace accel
@@ -249,10 +283,29 @@ int accel_opt_state_init(void *dev_state, const accel_hparams *hp, uint64_t glob
                          static_cast<cudaStream_t>(stream));
 }
 
+int accel_opt_state_advance(void *dev_state, const accel_hparams *hp, int is_adam,
+                            accel_stream_t stream) {
+  if (!dev_state || !hp) return fail(ACCEL_ERR_INVALID, "dev_state/hparams is NULL");
+  if (reinterpret_cast<uintptr_t>(dev_state) & 15)
+    return fail(ACCEL_ERR_ALIGN, "dev_state must be 16-byte aligned");
+  return launch_opt_advance(dev_state, hp->beta1, hp->beta2, is_adam != 0,
+                            static_cast<cudaStream_t>(stream));
+}
+
 int accel_apply_dev_state(accel_ctx *ctx, int task, int optimizer, float *var, float *slot0,
                           float *slot1, const void *const *grads, int n_workers, int grad_dtype,
                           uint64_t count, const accel_hparams *hp, const float *grad_sumsq_dev,
                           void *dev_state, accel_stream_t stream) {
+  return accel_apply_dev_state_ex(ctx, task, optimizer, var, slot0, slot1, grads, n_workers,
+                                  grad_dtype, count, hp, grad_sumsq_dev, dev_state, /*advance=*/1,
+                                  stream);
+}
+
+int accel_apply_dev_state_ex(accel_ctx *ctx, int task, int optimizer, float *var, float *slot0,
+                             float *slot1, const void *const *grads, int n_workers,
+                             int grad_dtype, uint64_t count, const accel_hparams *hp,
+                             const float *grad_sumsq_dev, void *dev_state, int advance,
+                             accel_stream_t stream) {
   if (optimizer < ACCEL_OPT_SGD || optimizer > ACCEL_OPT_ADAM)
     return fail(ACCEL_ERR_INVALID, "unknown optimizer %d", optimizer);
   if (!dev_state) return fail(ACCEL_ERR_INVALID, "dev_state is NULL");
@@ -263,7 +316,7 @@ int accel_apply_dev_state(accel_ctx *ctx, int task, int optimizer, float *var, f
                         optimizer == ACCEL_OPT_ADAM ? slot1 : nullptr, grads, n_workers,
                         grad_dtype, count, hp, grad_sumsq_dev, stream,
                         static_cast<const float *>(dev_state));
-  if (rc) return rc;
+  if (rc || !advance) return rc;
   return launch_opt_advance(dev_state, hp->beta1, hp->beta2, optimizer == ACCEL_OPT_ADAM,
                             static_cast<cudaStream_t>(stream));
 }
@@ -297,29 +350,6 @@ int accel_grad_sumsq(accel_ctx *ctx, int task, const void *const *grads, int n_w
 }
 
 // ---- the host-buffer step ---------------------------------------------------
-static int ensure_host_step(TaskState &ts, size_t stage_bytes) {
-  if (!ts.copy_in) {
-    ACCEL_CUDA(cudaStreamCreateWithFlags(&ts.copy_in, cudaStreamNonBlocking));
-    ACCEL_CUDA(cudaStreamCreateWithFlags(&ts.compute, cudaStreamNonBlocking));
-    ACCEL_CUDA(cudaStreamCreateWithFlags(&ts.copy_out, cudaStreamNonBlocking));
-    for (int i = 0; i < 2; ++i) {
-      ACCEL_CUDA(cudaEventCreateWithFlags(&ts.ev_in[i], cudaEventDisableTiming));
-      ACCEL_CUDA(cudaEventCreateWithFlags(&ts.ev_free[i], cudaEventDisableTiming));
-      ACCEL_CUDA(cudaEventCreateWithFlags(&ts.ev_done[i], cudaEventDisableTiming));
-    }
-  }
-  if (ts.stage_bytes < stage_bytes) {
-    for (int i = 0; i < 2; ++i) {
-      if (ts.stage_buf[i]) ACCEL_CUDA(cudaFree(ts.stage_buf[i]));
-      ts.stage_buf[i] = nullptr;
-    }
-    ts.stage_bytes = 0;
-    for (int i = 0; i < 2; ++i) ACCEL_CUDA(cudaMalloc(&ts.stage_buf[i], stage_bytes));
-    ts.stage_bytes = stage_bytes;
-  }
-  return ACCEL_OK;
-}
-
 int accel_ps_step_host(accel_ctx *ctx, int task, int optimizer, float *var, float *slot0,
                        float *slot1, const void *const *host_grads, int n_workers, int grad_dtype,
                        uint64_t count, const accel_hparams *hp, float *host_var_out) {
@@ -348,40 +378,52 @@ int accel_ps_step_host(accel_ctx *ctx, int task, int optimizer, float *var, floa
   rc = ensure_host_step(*ts, per_worker * n_workers);
   if (rc) return rc;
 
+  for (int w = 0; w < n_workers; ++w)
+    if (!host_grads[w]) return fail(ACCEL_ERR_INVALID, "host_grads[%d] is NULL", w);
   const uint64_t n_chunks = (count + chunk - 1) / chunk;
-  for (uint64_t k = 0; k < n_chunks; ++k) {
-    const int b = static_cast<int>(k & 1);
-    const uint64_t off = k * chunk;
-    const uint64_t n = std::min<uint64_t>(chunk, count - off);
-    // copy-in: wait until the kernel that last read this staging buffer is done
-    if (k >= 2) ACCEL_CUDA(cudaStreamWaitEvent(ts->copy_in, ts->ev_free[b], 0));
-    const void *dev_grads[ACCEL_MAX_WORKERS];
-    for (int w = 0; w < n_workers; ++w) {
-      if (!host_grads[w]) return fail(ACCEL_ERR_INVALID, "host_grads[%d] is NULL", w);
-      char *dst = static_cast<char *>(ts->stage_buf[b]) + per_worker * w;
-      const char *src = static_cast<const char *>(host_grads[w]) + off * gsize;
-      ACCEL_CUDA(cudaMemcpyAsync(dst, src, n * gsize, cudaMemcpyHostToDevice, ts->copy_in));
-      dev_grads[w] = dst;
+  // the pipeline proper; any failure falls through to the drain below so that no copy or
+  // kernel is still in flight on the caller's host buffers when the call returns
+  auto enqueue = [&]() -> int {
+    for (uint64_t k = 0; k < n_chunks; ++k) {
+      const int b = static_cast<int>(k & 1);
+      const uint64_t off = k * chunk;
+      const uint64_t n = std::min<uint64_t>(chunk, count - off);
+      // copy-in: wait until the kernel that last read this staging buffer is done
+      if (k >= 2) ACCEL_CUDA(cudaStreamWaitEvent(ts->copy_in, ts->ev_free[b], 0));
+      const void *dev_grads[ACCEL_MAX_WORKERS];
+      for (int w = 0; w < n_workers; ++w) {
+        char *dst = static_cast<char *>(ts->stage_buf[b]) + per_worker * w;
+        const char *src = static_cast<const char *>(host_grads[w]) + off * gsize;
+        ACCEL_CUDA(cudaMemcpyAsync(dst, src, n * gsize, cudaMemcpyHostToDevice, ts->copy_in));
+        dev_grads[w] = dst;
+      }
+      ACCEL_CUDA(cudaEventRecord(ts->ev_in[b], ts->copy_in));
+      // compute
+      ACCEL_CUDA(cudaStreamWaitEvent(ts->compute, ts->ev_in[b], 0));
+      int rc2 = apply_common(ctx, task, optimizer, var + off, slot0 ? slot0 + off : nullptr,
+                             slot1 ? slot1 + off : nullptr, dev_grads, n_workers, grad_dtype, n, hp,
+                             nullptr, ts->compute);
+      if (rc2) return rc2;
+      ACCEL_CUDA(cudaEventRecord(ts->ev_free[b], ts->compute));
+      // copy-out: the pull of the updated chunk
+      if (host_var_out) {
+        ACCEL_CUDA(cudaEventRecord(ts->ev_done[b], ts->compute));
+        ACCEL_CUDA(cudaStreamWaitEvent(ts->copy_out, ts->ev_done[b], 0));
+        ACCEL_CUDA(cudaMemcpyAsync(host_var_out + off, var + off, n * sizeof(float),
+                                   cudaMemcpyDeviceToHost, ts->copy_out));
+      }
     }
-    ACCEL_CUDA(cudaEventRecord(ts->ev_in[b], ts->copy_in));
-    // compute
-    ACCEL_CUDA(cudaStreamWaitEvent(ts->compute, ts->ev_in[b], 0));
-    rc = apply_common(ctx, task, optimizer, var + off, slot0 ? slot0 + off : nullptr,
-                      slot1 ? slot1 + off : nullptr, dev_grads, n_workers, grad_dtype, n, hp,
-                      nullptr, ts->compute);
-    if (rc) return rc;
-    ACCEL_CUDA(cudaEventRecord(ts->ev_free[b], ts->compute));
-    // copy-out: the pull of the updated chunk
-    if (host_var_out) {
-      ACCEL_CUDA(cudaEventRecord(ts->ev_done[b], ts->compute));
-      ACCEL_CUDA(cudaStreamWaitEvent(ts->copy_out, ts->ev_done[b], 0));
-      ACCEL_CUDA(cudaMemcpyAsync(host_var_out + off, var + off, n * sizeof(float),
-                                 cudaMemcpyDeviceToHost, ts->copy_out));
-    }
-  }
-  ACCEL_CUDA(cudaStreamSynchronize(ts->copy_in));
-  ACCEL_CUDA(cudaStreamSynchronize(ts->compute));
-  ACCEL_CUDA(cudaStreamSynchronize(ts->copy_out));
+    return ACCEL_OK;
+  };
+  rc = enqueue();
+  // drain all three streams on success AND on failure
+  const cudaError_t e1 = cudaStreamSynchronize(ts->copy_in);
+  const cudaError_t e2 = cudaStreamSynchronize(ts->compute);
+  const cudaError_t e3 = cudaStreamSynchronize(ts->copy_out);
+  if (rc) return rc;   // g_err holds the first failure's message
+  if (e1 != cudaSuccess) return fail_cuda(e1, "cudaStreamSynchronize(copy_in)");
+  if (e2 != cudaSuccess) return fail_cuda(e2, "cudaStreamSynchronize(compute)");
+  if (e3 != cudaSuccess) return fail_cuda(e3, "cudaStreamSynchronize(copy_out)");
   return ACCEL_OK;
 }
 

@@ -24,6 +24,8 @@ struct Tuning {
   int threads = 0;
   int ctas_per_sm = 0;
   int unroll = 0;
+  int reducer_pct = 0;  // in-switch step: share of CTAs that reduce+apply+pull (0 = default 25)
+  int coop = 1;         // one-kernel step: cooperative launch (0: plain launch for grids <= SMs)
 };
 
 constexpr int kReducePartials = 4096;  // upper bound on CTAs of the sum-of-squares grid
@@ -44,9 +46,12 @@ struct TaskState {
   void *stage_buf[2] = {nullptr, nullptr};
   size_t stage_bytes = 0;
   cudaEvent_t ev_in[2] = {nullptr, nullptr}, ev_free[2] = {nullptr, nullptr};
-  cudaEvent_t ev_done[2] = {nullptr, nullptr}, ev_out[2] = {nullptr, nullptr};
-  float *out_buf[2] = {nullptr, nullptr};
-  size_t out_bytes = 0;
+  cudaEvent_t ev_done[2] = {nullptr, nullptr};
+  // sharded host-buffer step: full-arena device copies of the local workers' gradients
+  void *host_step_grads = nullptr;
+  size_t host_step_grad_bytes = 0;
+  static constexpr int kHostSlices = 64;
+  cudaEvent_t ev_slice_in[kHostSlices] = {}, ev_slice_done[kHostSlices] = {};
   unsigned int shard_epoch = 0;  // barrier generation of the multi-GPU step
   cudaStream_t shard_aux = nullptr;  // apply_pull of slice k runs here beside push of slice k+1
   cudaEvent_t shard_ev_push = nullptr, shard_ev_done = nullptr;
@@ -64,6 +69,7 @@ struct accel_ctx {
 namespace accel {
 
 int task_state(accel_ctx *ctx, int task, TaskState **out);  // sets the device
+int ensure_host_streams(TaskState &ts);  // copy_in / compute / copy_out + their events
 
 // ---- kernel parameter blocks (passed by value as __grid_constant__) --------
 struct ApplyArgs {

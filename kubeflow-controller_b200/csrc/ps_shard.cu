@@ -55,6 +55,20 @@ __global__ void __launch_bounds__(512) ps_push(const __grid_constant__ ShardArgs
       item[j] = static_cast<uint64_t>(owner[j]) * shard_items + within;
       dst[j] = static_cast<uint64_t>(a.rank) * shard_items + within;
     }
+    if constexpr (sizeof(G) == 2 && NW == 1) {
+      if (a.stage_bf16) {
+        // one bf16 gradient per rank: the partial IS the gradient — forward the raw item
+        uint32_t raw[U][4];
+#pragma unroll
+        for (int j = 0; j < U; ++j)
+          if (ok[j]) ldg_stream_128u(static_cast<const uint16_t *>(a.grad[0]) + item[j] * 8, raw[j]);
+#pragma unroll
+        for (int j = 0; j < U; ++j)
+          if (ok[j])
+            st_128u(reinterpret_cast<uint16_t *>(a.stage[owner[j]]) + dst[j] * 8, raw[j]);
+        continue;
+      }
+    }
     if constexpr (NW > 0) {
       float g[NW][U][8];
 #pragma unroll
@@ -135,8 +149,7 @@ __global__ void __launch_bounds__(512) ps_apply_pull(const __grid_constant__ Sha
         float g[4][8];
 #pragma unroll
         for (int k = 0; k < 4; ++k)
-          if (s0i + k < a.world)
-            ld_256_plain(stage + (static_cast<uint64_t>(s0i + k) * shard_items + it) * 8, g[k]);
+          if (s0i + k < a.world) ld_stage_item(a, stage, s0i + k, shard_items, it, g[k]);
 #pragma unroll
         for (int k = 0; k < 4; ++k)
           if (s0i + k < a.world)
@@ -209,9 +222,14 @@ int fill_peers(const accel_peers *peers, uint64_t sub_begin, uint64_t sub_count,
     a->var[r] = peers->var[r];
     a->flags[r] = peers->flags[r];
   }
-  if (reinterpret_cast<uintptr_t>(peers->var_multicast) & 31)
-    return fail(ACCEL_ERR_ALIGN, "var_multicast must be 32-byte aligned");
+  if ((reinterpret_cast<uintptr_t>(peers->var_multicast) |
+       reinterpret_cast<uintptr_t>(peers->stage_multicast)) & 31)
+    return fail(ACCEL_ERR_ALIGN, "var_multicast / stage_multicast must be 32-byte aligned");
   a->var_mc = peers->var_multicast;
+  a->stage_mc = peers->stage_multicast;
+  if (peers->stage_dtype != ACCEL_F32 && peers->stage_dtype != ACCEL_BF16)
+    return fail(ACCEL_ERR_INVALID, "unknown stage_dtype %d", peers->stage_dtype);
+  a->stage_bf16 = peers->stage_dtype == ACCEL_BF16;
   if (peers->var_bf16) {
     for (int r = 0; r < peers->world; ++r) {
       if (!peers->var_bf16[r]) return fail(ACCEL_ERR_INVALID, "peer %d has a NULL var_bf16", r);
@@ -244,6 +262,10 @@ int fill_grads(const void *const *grads, int n_workers, int grad_dtype, ShardArg
     a->grad[w] = grads[w];
   }
   a->n_workers = n_workers;
+  if (a->stage_bf16 && !(grad_dtype == ACCEL_BF16 && n_workers == 1))
+    return fail(ACCEL_ERR_INVALID,
+                "stage_dtype ACCEL_BF16 carries ONE raw bf16 gradient per rank; got n_workers %d, "
+                "grad_dtype %d", n_workers, grad_dtype);
   return ACCEL_OK;
 }
 
@@ -445,6 +467,126 @@ int accel_shard_step(accel_ctx *ctx, const accel_peers *peers, int optimizer, fl
   ACCEL_CUDA(cudaEventRecord(ts->shard_ev_done, ts->shard_aux));
   ACCEL_CUDA(cudaStreamWaitEvent(s, ts->shard_ev_done, 0));
   return do_wait_pull(ctx, peers, epoch, s);
+}
+
+// `rows` runs of `width` bytes, `pitch` bytes apart on both sides. One 2-D copy while the pitch
+// is within the runtime's limit for pitched copies, one 1-D copy per row beyond it.
+static int copy_rows(void *dst, const void *src, size_t pitch, size_t width, int rows,
+                     cudaMemcpyKind kind, cudaStream_t s) {
+  if (rows == 1 || width == pitch) {
+    ACCEL_CUDA(cudaMemcpyAsync(dst, src, width == pitch ? pitch * rows : width, kind, s));
+    return ACCEL_OK;
+  }
+  if (pitch < (size_t{1} << 30)) {
+    ACCEL_CUDA(cudaMemcpy2DAsync(dst, pitch, src, pitch, width, rows, kind, s));
+    return ACCEL_OK;
+  }
+  for (int r = 0; r < rows; ++r)
+    ACCEL_CUDA(cudaMemcpyAsync(static_cast<char *>(dst) + pitch * r,
+                               static_cast<const char *>(src) + pitch * r, width, kind, s));
+  return ACCEL_OK;
+}
+
+int accel_shard_step_host(accel_ctx *ctx, const accel_peers *peers, int optimizer, float *slot0,
+                          float *slot1, const void *const *host_grads, int n_workers,
+                          int grad_dtype, int n_contrib, const accel_hparams *hp,
+                          float *host_var_out, int n_slices) {
+  ShardArgs a;
+  int rc = fill_peers(peers, 0, 0, &a);
+  if (rc) return rc;
+  TaskState *ts = nullptr;
+  rc = task_state(ctx, peers->rank, &ts);
+  if (rc) return rc;
+  if (!hp) return fail(ACCEL_ERR_INVALID, "hparams is NULL");
+  if (hp->clip_norm > 0.0f)
+    return fail(ACCEL_ERR_INVALID,
+                "accel_shard_step_host streams the gradient in slices and cannot clip by global "
+                "norm; clip_norm must be 0");
+  if (!host_grads) return fail(ACCEL_ERR_INVALID, "host_grads is NULL");
+  if (n_workers < 1 || n_workers > ACCEL_MAX_WORKERS)
+    return fail(ACCEL_ERR_INVALID, "n_workers %d out of range [1,%d]", n_workers,
+                ACCEL_MAX_WORKERS);
+  if (grad_dtype != ACCEL_F32 && grad_dtype != ACCEL_BF16)
+    return fail(ACCEL_ERR_INVALID, "unknown grad_dtype %d", grad_dtype);
+  for (int w = 0; w < n_workers; ++w)
+    if (!host_grads[w]) return fail(ACCEL_ERR_INVALID, "host_grads[%d] is NULL", w);
+  if (n_slices < 1 || n_slices > TaskState::kHostSlices)
+    return fail(ACCEL_ERR_INVALID, "n_slices %d out of range [1,%d]", n_slices,
+                TaskState::kHostSlices);
+  const size_t gsize = grad_dtype == ACCEL_BF16 ? 2 : 4;
+  const uint64_t shard = peers->shard_elems;
+  const int world = peers->world;
+  const size_t arena_bytes = (static_cast<size_t>(shard) * world * gsize + 255) & ~size_t{255};
+  rc = ensure_host_streams(*ts);
+  if (rc) return rc;
+  if (ts->host_step_grad_bytes < arena_bytes * n_workers) {
+    if (ts->host_step_grads) ACCEL_CUDA(cudaFree(ts->host_step_grads));
+    ts->host_step_grads = nullptr;
+    ts->host_step_grad_bytes = 0;
+    ACCEL_CUDA(cudaMalloc(&ts->host_step_grads, arena_bytes * n_workers));
+    ts->host_step_grad_bytes = arena_bytes * n_workers;
+  }
+  for (int k = 0; k < n_slices; ++k) {
+    if (!ts->ev_slice_in[k])
+      ACCEL_CUDA(cudaEventCreateWithFlags(&ts->ev_slice_in[k], cudaEventDisableTiming));
+    if (!ts->ev_slice_done[k])
+      ACCEL_CUDA(cudaEventCreateWithFlags(&ts->ev_slice_done[k], cudaEventDisableTiming));
+  }
+  const void *dev_grads[ACCEL_MAX_WORKERS];
+  for (int w = 0; w < n_workers; ++w)
+    dev_grads[w] = static_cast<char *>(ts->host_step_grads) + arena_bytes * w;
+  uint64_t per = (shard / 8 + n_slices - 1) / n_slices * 8;
+  if (per == 0) per = 8;
+
+  auto enqueue = [&]() -> int {
+    uint32_t epoch = 0;
+    int k = 0;
+    for (uint64_t begin = 0; begin < shard; begin += per, ++k) {
+      const uint64_t n = begin + per <= shard ? per : shard - begin;
+      // in: this slice of every shard of every local worker's gradient, over PCIe
+      for (int w = 0; w < n_workers; ++w) {
+        int rc2 = copy_rows(static_cast<char *>(const_cast<void *>(dev_grads[w])) + begin * gsize,
+                            static_cast<const char *>(host_grads[w]) + begin * gsize,
+                            shard * gsize, n * gsize, world, cudaMemcpyHostToDevice, ts->copy_in);
+        if (rc2) return rc2;
+      }
+      ACCEL_CUDA(cudaEventRecord(ts->ev_slice_in[k], ts->copy_in));
+      ACCEL_CUDA(cudaStreamWaitEvent(ts->compute, ts->ev_slice_in[k], 0));
+      // the step on this slice: push (sum + reduce-scatter), apply + pull (all-gather)
+      int rc2 = do_push(ctx, peers, dev_grads, n_workers, grad_dtype, begin, n, ts->compute, &epoch);
+      if (rc2) return rc2;
+      rc2 = do_apply_pull(ctx, peers, optimizer, slot0, slot1, n_contrib, hp, nullptr, begin, n,
+                          epoch, ts->compute);
+      if (rc2) return rc2;
+      if (host_var_out) {
+        // out: once every rank's pull of this slice has landed in the local replica
+        rc2 = do_wait_pull(ctx, peers, epoch, ts->compute);
+        if (rc2) return rc2;
+        ACCEL_CUDA(cudaEventRecord(ts->ev_slice_done[k], ts->compute));
+        ACCEL_CUDA(cudaStreamWaitEvent(ts->copy_out, ts->ev_slice_done[k], 0));
+        rc2 = copy_rows(host_var_out + begin, a.var[a.rank] + begin, shard * sizeof(float),
+                        n * sizeof(float), world, cudaMemcpyDeviceToHost, ts->copy_out);
+        if (rc2) return rc2;
+      }
+    }
+    if (!host_var_out) return do_wait_pull(ctx, peers, epoch, ts->compute);
+    return ACCEL_OK;
+  };
+  rc = enqueue();
+  const cudaError_t e1 = cudaStreamSynchronize(ts->copy_in);
+  const cudaError_t e2 = cudaStreamSynchronize(ts->compute);
+  const cudaError_t e3 = cudaStreamSynchronize(ts->copy_out);
+  if (rc) return rc;
+  if (e1 != cudaSuccess) return fail_cuda(e1, "cudaStreamSynchronize(copy_in)");
+  if (e2 != cudaSuccess) return fail_cuda(e2, "cudaStreamSynchronize(compute)");
+  if (e3 != cudaSuccess) return fail_cuda(e3, "cudaStreamSynchronize(copy_out)");
+  uint32_t status = 0;
+  ACCEL_CUDA(cudaMemcpy(&status, a.flags[a.rank] + kFlagStatus, sizeof(status),
+                        cudaMemcpyDeviceToHost));
+  if (status != 0)
+    return fail(ACCEL_ERR_STATE, "rank %d timed out waiting for rank %u during the host-buffer step",
+                a.rank, (status >> 8) & 0xff);
+  return ACCEL_OK;
 }
 
 int accel_shard_check(accel_ctx *ctx, const accel_peers *peers, accel_stream_t stream) {

@@ -27,6 +27,8 @@ struct ShardArgs {
   float *slot1;
   const float *sumsq;
   float *var_mc;   // multicast mapping of all ranks' var replicas, or nullptr
+  float *stage_mc; // multicast mapping of all ranks' stage buffers (in-switch step), or nullptr
+  int stage_bf16;  // stage slots hold raw bf16 (one bf16 gradient per rank); else fp32 partials
   uint16_t *var_bf16[ACCEL_MAX_PS];  // bf16 replicas (pull target) or all nullptr
   uint64_t shard;  // elements per shard, multiple of 8
   uint64_t sub_begin, sub_count;  // the slice of EVERY shard this launch covers (multiples of 8)
@@ -139,6 +141,33 @@ __device__ __forceinline__ void pull_item(const ShardArgs &a, uint64_t var_elem,
       if (p >= a.world) p -= a.world;
       st_256(a.var[p] + var_elem, v);
     }
+  }
+}
+__device__ __forceinline__ void ld_256_plain(const float *p, float (&o)[8]);
+// 8 raw bf16 values (one 128-bit load) written by a peer during this step: coherent path
+__device__ __forceinline__ void ld_128u_plain(const uint16_t *p, uint32_t (&o)[4]) {
+  asm volatile("ld.global.L1::no_allocate.v4.b32 {%0,%1,%2,%3}, [%4];"
+               : "=r"(o[0]), "=r"(o[1]), "=r"(o[2]), "=r"(o[3])
+               : "l"(p)
+               : "memory");
+}
+__device__ __forceinline__ void widen_bf16x8(const uint32_t (&u)[4], float (&o)[8]) {
+#pragma unroll
+  for (int k = 0; k < 4; ++k) {
+    o[2 * k] = bf16_lo(u[k]);
+    o[2 * k + 1] = bf16_hi(u[k]);
+  }
+}
+// One item (8 elements) of stage slot `slot` of shard-local item `it`, as fp32.
+__device__ __forceinline__ void ld_stage_item(const ShardArgs &a, const float *stage, int slot,
+                                              uint64_t shard_items, uint64_t it, float (&o)[8]) {
+  const uint64_t idx = (static_cast<uint64_t>(slot) * shard_items + it) * 8;
+  if (a.stage_bf16) {
+    uint32_t u[4];
+    ld_128u_plain(reinterpret_cast<const uint16_t *>(stage) + idx, u);
+    widen_bf16x8(u, o);
+  } else {
+    ld_256_plain(stage + idx, o);
   }
 }
 __device__ __forceinline__ void ld_256_plain(const float *p, float (&o)[8]) {

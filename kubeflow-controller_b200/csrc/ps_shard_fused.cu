@@ -18,40 +18,9 @@
 //
 // R > 1 emulates R ranks that live on ONE GPU inside a single cooperative launch (CTA group
 // g plays rank g): the single-GPU test vehicle for the same code path.
-#include <cooperative_groups.h>
-
-#include "ps_shard.cuh"
+#include "ps_shard_fused.cuh"
 
 namespace accel {
-
-constexpr int kFusedThreads = 256;
-constexpr int kMaxSlices = 64;
-constexpr int kEmuRanks = 8;
-
-template <int R>
-struct FusedArgs {
-  ShardArgs r[R];
-  int ctas_per_rank;
-  int n_slices;
-  int roles;  // ACCEL_OVERLAP_ROLES: even CTAs only push, odd CTAs only apply+pull
-  uint32_t epoch_base;  // slice k is published as epoch_base + k + 1, the pull as epoch_base + n_slices
-};
-
-// Non-blocking: have all ranks published >= target in words [base, base+world)?
-__device__ inline bool poll_all(uint32_t *flags, int base, int world, uint32_t target) {
-  __shared__ int ready;
-  if (threadIdx.x == 0) {
-    int ok = 1;
-    for (int s = 0; s < world; ++s)
-      ok &= static_cast<int32_t>(ld_relaxed_sys(flags + base + s) - target) >= 0;
-    if (ok) __threadfence_system();   // the relaxed observations become an acquire
-    ready = ok;
-  }
-  __syncthreads();
-  const bool r = ready != 0;
-  __syncthreads();  // `ready` may be rewritten by the next poll
-  return r;
-}
 
 template <typename G, int NW>
 __device__ __forceinline__ void push_slice(const ShardArgs &a, uint64_t sub_first,
@@ -70,6 +39,15 @@ __device__ __forceinline__ void push_slice(const ShardArgs &a, uint64_t sub_firs
     if (c >= a.world) c -= a.world;
     const uint64_t within = sub_first + in_shard;
     const uint64_t item = static_cast<uint64_t>(c) * shard_items + within;
+    if constexpr (sizeof(G) == 2 && NW == 1) {
+      if (a.stage_bf16) {   // one bf16 gradient per rank: forward the raw item (2 B/elem)
+        uint32_t raw[4];
+        ldg_stream_128u(static_cast<const uint16_t *>(a.grad[0]) + item * 8, raw);
+        st_128u(reinterpret_cast<uint16_t *>(a.stage[c]) +
+                    (static_cast<uint64_t>(a.rank) * shard_items + within) * 8, raw);
+        continue;
+      }
+    }
     float acc[8];
     if constexpr (NW > 0) {
       float g[NW][8];
@@ -118,8 +96,7 @@ __device__ __forceinline__ void apply_slice(const ShardArgs &a, const Scalars &s
       float g[4][8];
 #pragma unroll
       for (int q = 0; q < 4; ++q)
-        if (s0i + q < a.world)
-          ld_256_plain(stage + (static_cast<uint64_t>(s0i + q) * shard_items + it) * 8, g[q]);
+        if (s0i + q < a.world) ld_stage_item(a, stage, s0i + q, shard_items, it, g[q]);
 #pragma unroll
       for (int q = 0; q < 4; ++q)
         if (s0i + q < a.world)
@@ -143,20 +120,7 @@ __global__ void __launch_bounds__(kFusedThreads, 2)
   const int bid = R == 1 ? blockIdx.x : blockIdx.x - vr * nb;
   uint32_t *flags = a.flags[a.rank];
 
-  ApplyArgs sa;  // scalars only
-  sa.sumsq = a.sumsq;
-  sa.dev_powers = nullptr;
-  sa.use_nesterov = a.use_nesterov;
-  sa.lr = a.lr;
-  sa.momentum = a.momentum;
-  sa.beta1 = a.beta1;
-  sa.one_minus_beta1 = a.one_minus_beta1;
-  sa.one_minus_beta2 = a.one_minus_beta2;
-  sa.alpha = a.alpha;
-  sa.epsilon = a.epsilon;
-  sa.mean_div = a.mean_div;
-  sa.clip_norm = a.clip_norm;
-  const Scalars sc = make_scalars(sa);
+  const Scalars sc = shard_scalars(a);
 
   const uint64_t shard_items = a.shard / 8;
   const int S = fa.n_slices;
@@ -193,7 +157,7 @@ __global__ void __launch_bounds__(kFusedThreads, 2)
     } else {
       // Applier: blocks (bounded) only on OTHER CTAs' pushes, which never block.
       for (int k = 0; k < S; ++k) {
-        if (!wait_all(flags, kFlagPush, a.world, fa.epoch_base + k + 1)) return;
+        if (!wait_all(flags, kFlagPush, a.world, fa.epoch_base + k + 1)) break;   // timed out
         apply_slice<OPT>(a, sc, slice_first(k), slice_items(k), rb, n_apply);
       }
     }
@@ -223,51 +187,26 @@ __global__ void __launch_bounds__(kFusedThreads, 2)
     }
     // all pushes of this CTA are issued: now it may block for what is still missing
     for (; next_apply < S; ++next_apply) {
-      if (!wait_all(flags, kFlagPush, a.world, fa.epoch_base + next_apply + 1)) return;
+      if (!wait_all(flags, kFlagPush, a.world, fa.epoch_base + next_apply + 1)) break;   // timed out
       apply_slice<OPT>(a, sc, slice_first(next_apply), slice_items(next_apply), bid, nb);
     }
   }
   // pull signal, then the closing wait by the CTA that took the last ticket
-  __syncthreads();
-  __shared__ int last;
-  if (threadIdx.x == 0) {
-    __threadfence_system();
-    const unsigned int done = atomicAdd(flags + kFlagTicketApply, 1u);
-    last = done == static_cast<unsigned int>(nb) - 1;
-    if (last) {
-      flags[kFlagTicketApply] = 0;
-      __threadfence_system();
-      for (int p = 0; p < a.world; ++p)
-        st_relaxed_sys(a.flags[p] + kFlagPull + a.rank, fa.epoch_base + S);
-    }
-  }
-  __syncthreads();
-  if (last) wait_all(flags, kFlagPull, a.world, fa.epoch_base + S);
+  close_step(a, flags, nb, fa.epoch_base + S);
 }
 
 template <typename G, int NW, int OPT, int R>
 static int launch_fused_one(const FusedArgs<R> &fa_in, int n_ranks, const TaskState &ts,
-                            int ctas_per_sm_cap, cudaStream_t s) {
-  auto kern = ps_step_fused<G, NW, OPT, R>;
-  int per_sm = 0;
-  ACCEL_CUDA(cudaOccupancyMaxActiveBlocksPerMultiprocessor(&per_sm, kern, kFusedThreads, 0));
-  if (per_sm < 1) return fail(ACCEL_ERR_CUDA, "fused step kernel does not fit on an SM");
-  if (per_sm > ctas_per_sm_cap) per_sm = ctas_per_sm_cap;
+                            const Tuning &tune, cudaStream_t s) {
   FusedArgs<R> fa = fa_in;
-  const int resident = per_sm * ts.sm_count;
-  fa.ctas_per_rank = resident / n_ranks;
-  if (fa.ctas_per_rank < 1)
-    return fail(ACCEL_ERR_INVALID, "%d ranks do not fit in %d resident CTAs", n_ranks, resident);
-  void *params[] = {&fa};
-  ACCEL_CUDA(cudaLaunchCooperativeKernel(reinterpret_cast<void *>(kern),
-                                         dim3(fa.ctas_per_rank * n_ranks), dim3(kFusedThreads),
-                                         params, 0, s));
-  return ACCEL_OK;
+  const uint64_t items = fa.r[0].shard / 8 * fa.r[0].world;
+  return launch_resident<FusedArgs<R>>(ps_step_fused<G, NW, OPT, R>, fa, n_ranks, ts, 2, items, tune,
+                                       s);
 }
 
 template <typename G, int OPT, int R>
-static int launch_fused_nw(const FusedArgs<R> &fa, int n_ranks, const TaskState &ts, int cap,
-                           cudaStream_t s) {
+static int launch_fused_nw(const FusedArgs<R> &fa, int n_ranks, const TaskState &ts,
+                           const Tuning &cap, cudaStream_t s) {
   switch (fa.r[0].n_workers) {
     case 1: return launch_fused_one<G, 1, OPT, R>(fa, n_ranks, ts, cap, s);
     case 2: return launch_fused_one<G, 2, OPT, R>(fa, n_ranks, ts, cap, s);
@@ -279,7 +218,7 @@ static int launch_fused_nw(const FusedArgs<R> &fa, int n_ranks, const TaskState 
 
 template <int R>
 static int launch_fused(const FusedArgs<R> &fa, int n_ranks, int optimizer, int grad_dtype,
-                        const TaskState &ts, int cap, cudaStream_t s) {
+                        const TaskState &ts, const Tuning &cap, cudaStream_t s) {
   const bool bf = grad_dtype == ACCEL_BF16;
   switch (optimizer) {
     case ACCEL_OPT_SGD:
@@ -294,7 +233,7 @@ static int launch_fused(const FusedArgs<R> &fa, int n_ranks, int optimizer, int 
   }
 }
 
-static int fill_rank(const accel_peers *peers, int optimizer, float *slot0, float *slot1,
+int fill_rank(const accel_peers *peers, int optimizer, float *slot0, float *slot1,
                      const void *const *grads, int n_workers, int grad_dtype, int n_contrib,
                      const accel_hparams *hp, const float *sumsq, ShardArgs *a) {
   int rc = fill_peers(peers, 0, 0, a);
@@ -304,7 +243,7 @@ static int fill_rank(const accel_peers *peers, int optimizer, float *slot0, floa
   return fill_optimizer(optimizer, slot0, slot1, n_contrib, hp, sumsq, a);
 }
 
-static int clamp_slices(int n_slices, uint64_t shard_elems) {
+int clamp_slices(int n_slices, uint64_t shard_elems) {
   if (n_slices < 1) n_slices = 1;
   if (n_slices > kMaxSlices) n_slices = kMaxSlices;
   const uint64_t items = shard_elems / 8;
@@ -316,6 +255,28 @@ static int clamp_slices(int n_slices, uint64_t shard_elems) {
 
 using namespace accel;
 
+static bool overlap_ok(int overlap) {
+  return overlap == ACCEL_OVERLAP_INLINE || overlap == ACCEL_OVERLAP_ROLES ||
+         overlap == ACCEL_OVERLAP_SWITCH;
+}
+
+// SWITCH on real peers runs through the NVSwitch: both multicast mappings or neither.
+static int check_switch(const accel_peers *peers, const ShardArgs &a) {
+  if ((a.stage_mc == nullptr) != (a.var_mc == nullptr))
+    return fail(ACCEL_ERR_INVALID,
+                "ACCEL_OVERLAP_SWITCH needs stage_multicast AND var_multicast (or neither: the "
+                "peer-load form)");
+  if (a.var_bf16[0] != nullptr && a.var_mc != nullptr)
+    return fail(ACCEL_ERR_INVALID, "var_bf16 and the multicast pull are mutually exclusive");
+  (void)peers;
+  return ACCEL_OK;
+}
+
+static int reducers_for(const Tuning &t, int per_rank_hint) {
+  (void)per_rank_hint;
+  return t.reducer_pct > 0 ? t.reducer_pct : 25;
+}
+
 extern "C" {
 
 int accel_shard_step_fused(accel_ctx *ctx, const accel_peers *peers, int optimizer, float *slot0,
@@ -323,8 +284,7 @@ int accel_shard_step_fused(accel_ctx *ctx, const accel_peers *peers, int optimiz
                            int n_contrib, const accel_hparams *hp, const float *grad_sumsq_dev,
                            int n_slices, int overlap, accel_stream_t stream) {
   if (!peers) return fail(ACCEL_ERR_INVALID, "peers is NULL");
-  if (overlap != ACCEL_OVERLAP_INLINE && overlap != ACCEL_OVERLAP_ROLES)
-    return fail(ACCEL_ERR_INVALID, "unknown overlap %d", overlap);
+  if (!overlap_ok(overlap)) return fail(ACCEL_ERR_INVALID, "unknown overlap %d", overlap);
   TaskState *ts = nullptr;
   int rc = task_state(ctx, peers->rank, &ts);
   if (rc) return rc;
@@ -334,10 +294,21 @@ int accel_shard_step_fused(accel_ctx *ctx, const accel_peers *peers, int optimiz
   if (rc) return rc;
   fa.n_slices = clamp_slices(n_slices, peers->shard_elems);
   fa.roles = overlap == ACCEL_OVERLAP_ROLES;
+  fa.n_reducers = reducers_for(ctx->tuning, 0);   // percent; the launcher turns it into CTAs
   fa.epoch_base = ts->shard_epoch;
-  ts->shard_epoch += fa.n_slices;
   fa.ctas_per_rank = 0;
-  return launch_fused<1>(fa, 1, optimizer, grad_dtype, *ts, 2, static_cast<cudaStream_t>(stream));
+  cudaStream_t s = static_cast<cudaStream_t>(stream);
+  if (overlap == ACCEL_OVERLAP_SWITCH) {
+    rc = check_switch(peers, fa.r[0]);
+    if (rc) return rc;
+    rc = launch_switch(fa, optimizer, grad_dtype, *ts, ctx->tuning, s);
+  } else {
+    rc = launch_fused<1>(fa, 1, optimizer, grad_dtype, *ts, ctx->tuning, s);
+  }
+  // the epoch advances only once the step is really enqueued: a failed launch leaves this
+  // rank in step with its peers
+  if (rc == ACCEL_OK) ts->shard_epoch += fa.n_slices;
+  return rc;
 }
 
 int accel_shard_step_local_group(accel_ctx *ctx, const accel_peers *const *peers_of_rank,
@@ -346,8 +317,7 @@ int accel_shard_step_local_group(accel_ctx *ctx, const accel_peers *const *peers
                                  int n_workers, int grad_dtype, int n_contrib,
                                  const accel_hparams *hp, const float *grad_sumsq_dev,
                                  int n_slices, int overlap, accel_stream_t stream) {
-  if (overlap != ACCEL_OVERLAP_INLINE && overlap != ACCEL_OVERLAP_ROLES)
-    return fail(ACCEL_ERR_INVALID, "unknown overlap %d", overlap);
+  if (!overlap_ok(overlap)) return fail(ACCEL_ERR_INVALID, "unknown overlap %d", overlap);
   if (!peers_of_rank || !grads) return fail(ACCEL_ERR_INVALID, "peers_of_rank/grads is NULL");
   if (n_ranks < 1 || n_ranks > kEmuRanks)
     return fail(ACCEL_ERR_INVALID, "n_ranks %d out of range [1,%d]", n_ranks, kEmuRanks);
@@ -370,13 +340,47 @@ int accel_shard_step_local_group(accel_ctx *ctx, const accel_peers *const *peers
                    slot1 ? slot1[r] : nullptr, grads[r], n_workers, grad_dtype, n_contrib, hp,
                    grad_sumsq_dev, &fa.r[r]);
     if (rc) return rc;
+    if (overlap == ACCEL_OVERLAP_SWITCH && (fa.r[r].stage_mc || fa.r[r].var_mc))
+      return fail(ACCEL_ERR_INVALID,
+                  "a local group has no NVSwitch between its ranks: multicast pointers must be NULL");
   }
   fa.n_slices = clamp_slices(n_slices, peers_of_rank[0]->shard_elems);
   fa.roles = overlap == ACCEL_OVERLAP_ROLES;
+  fa.n_reducers = reducers_for(ctx->tuning, 0);
   fa.epoch_base = ts0->shard_epoch;
-  for (int r = 0; r < n_ranks; ++r) ctx->task[r].shard_epoch += fa.n_slices;
-  return launch_fused<kEmuRanks>(fa, n_ranks, optimizer, grad_dtype, *ts0, 2,
-                                 static_cast<cudaStream_t>(stream));
+  cudaStream_t s = static_cast<cudaStream_t>(stream);
+  const int rc = overlap == ACCEL_OVERLAP_SWITCH
+                     ? launch_switch_group(fa, n_ranks, optimizer, grad_dtype, *ts0, ctx->tuning, s)
+                     : launch_fused<kEmuRanks>(fa, n_ranks, optimizer, grad_dtype, *ts0,
+                                               ctx->tuning, s);
+  if (rc == ACCEL_OK)
+    for (int r = 0; r < n_ranks; ++r) ctx->task[r].shard_epoch += fa.n_slices;
+  return rc;
+}
+
+int accel_shard_reset(accel_ctx *ctx, const accel_peers *peers, accel_stream_t stream) {
+  ShardArgs a;
+  int rc = fill_peers(peers, 0, 0, &a);
+  if (rc) return rc;
+  TaskState *ts = nullptr;
+  rc = task_state(ctx, peers->rank, &ts);
+  if (rc) return rc;
+  cudaStream_t s = static_cast<cudaStream_t>(stream);
+  ACCEL_CUDA(cudaStreamSynchronize(s));
+  if (ts->shard_aux) ACCEL_CUDA(cudaStreamSynchronize(ts->shard_aux));
+  ACCEL_CUDA(cudaMemsetAsync(a.flags[a.rank], 0, ACCEL_SHARD_FLAG_WORDS * sizeof(uint32_t), s));
+  ACCEL_CUDA(cudaStreamSynchronize(s));
+  ts->shard_epoch = 0;
+  return ACCEL_OK;
+}
+
+int accel_ctx_set_step_shape(accel_ctx *ctx, int reducer_pct, int coop) {
+  if (!ctx) return fail(ACCEL_ERR_INVALID, "ctx is NULL");
+  if (reducer_pct < 0 || reducer_pct > 90)
+    return fail(ACCEL_ERR_INVALID, "reducer_pct %d out of range [0,90]", reducer_pct);
+  ctx->tuning.reducer_pct = reducer_pct;
+  ctx->tuning.coop = coop ? 1 : 0;
+  return ACCEL_OK;
 }
 
 }  // extern "C"

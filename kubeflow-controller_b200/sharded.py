@@ -120,9 +120,15 @@ class ShardedPS:
                  hp: accel.HParams, mode: str = "fused", ctx: accel.Context | None = None,
                  peer_ptrs=None, gpu_ordinals=None, n_chunks: int | None = None,
                  rendezvous: str = "ipc", multicast: bool = False, pull_dtype: str = "f32",
-                 overlap: int | None = None):
-        if mode not in ("fused", "streams", "nccl"):
+                 overlap: int | None = None, bf16_stage: bool = True):
+        if mode not in ("fused", "streams", "nccl", "switch"):
             raise ValueError(f"unknown mode {mode!r}")
+        if mode == "switch":
+            # the in-switch step is the one-kernel step with ACCEL_OVERLAP_SWITCH; on real peers
+            # it needs multicast mappings of stage AND var (symmetric-memory rendezvous)
+            if peer_ptrs is None and world > 1:
+                rendezvous, multicast = "symm", True
+            overlap = accel.OVERLAP_SWITCH
         if rendezvous not in ("ipc", "symm"):
             raise ValueError(f"unknown rendezvous {rendezvous!r}")
         if pull_dtype not in ("f32", "bf16"):
@@ -133,16 +139,24 @@ class ShardedPS:
         self.rank, self.world, self.mode = rank, world, mode
         # slices of the step: measured on B200, overlap pays at 2 ranks (4 slices: 0.817 ms vs
         # 0.874 ms) and costs at 8 (1 slice: 1.166 ms, 2: 1.184 ms, 4: 1.299 ms)
-        self.n_chunks = n_chunks or (4 if world <= 2 else 2 if world <= 4 else 1)
+        self.n_chunks = n_chunks or (8 if mode == "switch" else
+                                     4 if world <= 2 else 2 if world <= 4 else 1)
         # split roles measured faster at 2 ranks (0.773 vs 0.815 ms) and slower at 4 (1.012 vs 0.983)
         self.overlap = overlap if overlap is not None else \
             (accel.OVERLAP_ROLES if world <= 2 else accel.OVERLAP_INLINE)
         self.multicast_ptr = 0
+        self.stage_multicast_ptr = 0
+        self.bf16_stage = bf16_stage and mode != "nccl"
         self.device_index = device_index
         self.device = torch.device("cuda", device_index)
         self.optimizer, self.hp = optimizer, hp
         self.elems = elems
         self.padded, self.shard = shard_layout(elems, world)
+        if ctx is None and gpu_ordinals is None:
+            # task r <-> GPU r, except that THIS rank runs on the device it was given (local rank
+            # != rank on multi-node jobs or under a CUDA_VISIBLE_DEVICES remap)
+            gpu_ordinals = list(range(world))
+            gpu_ordinals[rank] = device_index
         self.ctx = ctx or accel.Context(world, gpu_ordinals)
         # the nccl-mode pre-sum is a world-of-one push on THIS rank's GPU
         self.solo_ctx = accel.Context(1, [device_index])
@@ -157,6 +171,11 @@ class ShardedPS:
                                  self.buf_flags.peer_ptrs))
             if multicast:
                 self.multicast_ptr = self.buf_var.multicast_ptr
+            if mode == "switch":
+                self.stage_multicast_ptr = self.buf_stage.multicast_ptr
+                if not (self.multicast_ptr and self.stage_multicast_ptr):
+                    raise RuntimeError("mode='switch' needs NVSwitch multicast mappings; the "
+                                       "symmetric-memory rendezvous returned none on this fabric")
         else:
             self.buf_var = DevBuffer(self.padded * 4, device_index)
             self.buf_stage = DevBuffer(self.padded * 4, device_index)
@@ -175,7 +194,8 @@ class ShardedPS:
                 if optimizer == accel.OPT_ADAM else None
             self.gshard = torch.empty(self.shard, device=self.device) if mode == "nccl" else None
         n_slices = -(-(self.shard // 8) // (-(-(self.shard // 8) // self.n_chunks)))
-        self.launches_per_step = {"fused": 1, "streams": 2 * n_slices + 1, "nccl": 2}[mode]
+        self.launches_per_step = {"fused": 1, "switch": 1, "streams": 2 * n_slices + 1,
+                                  "nccl": 2}[mode]
         if peer_ptrs is None:
             mine = (self.buf_var.export(), self.buf_stage.export(), self.buf_flags.export(),
                     self.buf_var16.export() if self.buf_var16 else None)
@@ -201,32 +221,46 @@ class ShardedPS:
         if self.pull_dtype == "bf16":
             self._var16_arr = (ctypes.c_void_p * w)(*[p[3] for p in peer_ptrs])
         self.peers = accel.Peers(self.rank, w, self.shard, self._stage_arr, self._var_arr,
-                                 self._flags_arr, self.multicast_ptr or None, self._var16_arr)
+                                 self._flags_arr, self.multicast_ptr or None, self._var16_arr,
+                                 self.stage_multicast_ptr or None, accel.F32, 0)
+        # the same view with raw-bf16 stage slots: used when a step pushes ONE bf16 gradient
+        self.peers_b16 = accel.Peers(self.rank, w, self.shard, self._stage_arr, self._var_arr,
+                                     self._flags_arr, self.multicast_ptr or None, self._var16_arr,
+                                     self.stage_multicast_ptr or None, accel.BF16, 0)
         # world = 1 view onto the same stage buffer: the local pre-sum of nccl mode
         self._solo_var = (ctypes.c_void_p * 1)(self.buf_var.ptr)
         self._solo_stage = (ctypes.c_void_p * 1)(self.buf_stage.ptr)
         self._solo_flags = (ctypes.c_void_p * 1)(self.buf_flags.ptr)
         self.solo = accel.Peers(0, 1, self.padded, self._solo_stage, self._solo_var,
-                                self._solo_flags, None, None)
+                                self._solo_flags, None, None, None, accel.F32, 0)
 
     @property
     def var_shard(self) -> torch.Tensor:
         return self.var[self.rank * self.shard:(self.rank + 1) * self.shard]
 
     # ---- the three phases (exposed so a single GPU can emulate several ranks in turn) ----
+    def peers_for(self, grads):
+        """The peer view a step with these gradients uses: raw-bf16 stage slots when every rank
+        pushes exactly one bf16 gradient (half the reduce-scatter bytes, same bits)."""
+        import torch
+        b16 = self.bf16_stage and len(grads) == 1 and grads[0].dtype == torch.bfloat16
+        self._last_peers = self.peers_b16 if b16 else self.peers
+        return self._last_peers
+
     def push(self, grads, stream=None, peers=None, sub=(0, 0)) -> int:
         """Returns the epoch this push opened."""
         ctx = self.solo_ctx if peers is self.solo else self.ctx
         epoch = ctypes.c_uint32()
         accel.check(self.lib.accel_shard_push(
-            ctx.handle, ctypes.byref(peers or self.peers), accel._grad_array(grads),
+            ctx.handle, ctypes.byref(peers or self.peers_for(grads)), accel._grad_array(grads),
             len(grads), accel._grad_dtype(grads[0]), sub[0], sub[1],
             accel._stream_handle(stream), ctypes.byref(epoch)))
         return epoch.value
 
     def apply_pull(self, n_contrib: int, sumsq=None, stream=None, sub=(0, 0), epoch=0):
         accel.check(self.lib.accel_shard_apply_pull(
-            self.ctx.handle, ctypes.byref(self.peers), self.optimizer, accel._ptr(self.slot0),
+            self.ctx.handle, ctypes.byref(getattr(self, "_last_peers", self.peers)),
+            self.optimizer, accel._ptr(self.slot0),
             accel._ptr(self.slot1), n_contrib, ctypes.byref(self.hp), accel._ptr(sumsq),
             sub[0], sub[1], epoch, accel._stream_handle(stream)))
 
@@ -238,7 +272,12 @@ class ShardedPS:
         """Sum of squares of THIS shard's aggregated gradient (the `world` stage slots summed in
         rank order) into out[0]; call after wait_push. Add the ranks' results for the global
         norm."""
-        slots = [self.stage[s * self.shard:(s + 1) * self.shard] for s in range(self.world)]
+        import torch
+        if getattr(self, "_last_peers", self.peers) is self.peers_b16:
+            st16 = self.stage.view(torch.bfloat16)      # raw-bf16 slots, `shard` elements apart
+            slots = [st16[s * self.shard:(s + 1) * self.shard] for s in range(self.world)]
+        else:
+            slots = [self.stage[s * self.shard:(s + 1) * self.shard] for s in range(self.world)]
         self.ctx.grad_sumsq(slots, out, aggregate=accel.AGG_SUM, task=self.rank,
                             count=self.shard, stream=stream)
 
@@ -255,6 +294,24 @@ class ShardedPS:
         """Synchronise and raise if a cross-GPU wait of this rank timed out."""
         accel.check(self.lib.accel_shard_check(self.ctx.handle, ctypes.byref(self.peers),
                                                accel._stream_handle(stream)))
+
+    def reset(self, stream=None):
+        """After a timeout (check() raised): zero this rank's flag words and restart its epoch.
+        Every rank must call it, with a barrier before the next step."""
+        accel.check(self.lib.accel_shard_reset(self.ctx.handle, ctypes.byref(self.peers),
+                                               accel._stream_handle(stream)))
+
+    def step_host(self, host_grads, host_var_out=None, n_slices=16):
+        """The step with this rank's worker gradients in pinned HOST memory
+        (accel_shard_step_host): H2D of slice k+1, the sharded step on slice k and the D2H of
+        slice k-1's part of the replica overlap; returns when the step is complete."""
+        n_contrib = len(host_grads) * self.world
+        accel.check(self.lib.accel_shard_step_host(
+            self.ctx.handle, ctypes.byref(self.peers_for(host_grads)), self.optimizer,
+            accel._ptr(self.slot0), accel._ptr(self.slot1), accel._grad_array(host_grads),
+            len(host_grads), accel._grad_dtype(host_grads[0]), n_contrib, ctypes.byref(self.hp),
+            accel._ptr(host_var_out), n_slices))
+        self.finish_step()
 
     def finish_step(self):
         if self.optimizer == accel.OPT_ADAM:
@@ -278,12 +335,12 @@ class ShardedPS:
                 dist.all_reduce(ss, op=dist.ReduceOp.SUM)
             self.apply_pull(n_contrib, ss, stream, epoch=epoch)
             self.wait_pull(stream, epoch)
-        elif self.mode in ("fused", "streams"):
-            head = (self.ctx.handle, ctypes.byref(self.peers), self.optimizer,
+        elif self.mode in ("fused", "streams", "switch"):
+            head = (self.ctx.handle, ctypes.byref(self.peers_for(grads)), self.optimizer,
                     accel._ptr(self.slot0), accel._ptr(self.slot1), accel._grad_array(grads),
                     len(grads), accel._grad_dtype(grads[0]), n_contrib, ctypes.byref(self.hp),
                     accel._ptr(sumsq), self.n_chunks)
-            if self.mode == "fused":      # one cooperative kernel
+            if self.mode in ("fused", "switch"):      # one cooperative kernel
                 accel.check(self.lib.accel_shard_step_fused(*head, self.overlap,
                                                             accel._stream_handle(stream)))
             else:                         # separate kernels, slices pipelined over two streams
@@ -301,7 +358,7 @@ class ShardedPS:
 
 
 def local_group(world: int, elems: int, optimizer: int, hp_factory, device_index: int = 0,
-                n_chunks: int = 1, pull_dtype: str = "f32"):
+                n_chunks: int = 1, pull_dtype: str = "f32", bf16_stage: bool = True):
     """`world` ranks emulated on ONE GPU inside one process (tests): every rank's buffers are
     plain local allocations and the phases are run rank after rank on one stream, so every
     device-side wait is already satisfied when its kernel starts."""
@@ -310,7 +367,7 @@ def local_group(world: int, elems: int, optimizer: int, hp_factory, device_index
     for r in range(world):
         ranks.append(ShardedPS(r, world, device_index, elems, optimizer, hp_factory(), ctx=ctx,
                                peer_ptrs=[(0, 0, 0, 0)] * world, n_chunks=n_chunks,
-                               pull_dtype=pull_dtype))
+                               pull_dtype=pull_dtype, bf16_stage=bf16_stage))
     ptrs = [(x.buf_var.ptr, x.buf_stage.ptr, x.buf_flags.ptr,
              x.buf_var16.ptr if x.buf_var16 else 0) for x in ranks]
     for x in ranks:
@@ -345,7 +402,7 @@ def local_group_step_fused(ranks, grads_per_rank, n_slices=None, stream=None, su
     x0 = ranks[0]
     n_contrib = sum(len(g) for g in grads_per_rank)
     PP = ctypes.POINTER(accel.Peers)
-    peers = (PP * n)(*[ctypes.pointer(x.peers) for x in ranks])
+    peers = (PP * n)(*[ctypes.pointer(x.peers_for(g)) for x, g in zip(ranks, grads_per_rank)])
     s0 = (ctypes.c_void_p * n)(*[accel._ptr(x.slot0) for x in ranks])
     s1 = (ctypes.c_void_p * n)(*[accel._ptr(x.slot1) for x in ranks])
     garr = [accel._grad_array(g) for g in grads_per_rank]

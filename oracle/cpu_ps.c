@@ -28,7 +28,7 @@
  * passes, Momentum = 2, aggregation = one pass per arriving gradient), fp32,
  * each operation rounded on its own (build with -ffp-contract=off: the stock
  * TF-1.4 wheel has no FMA). Passes are split over `threads` host threads by
- * contiguous ranges, as Eigen's ThreadPoolDevice does.
+ * contiguous ranges, as Eigen's ThreadPoolDevice does, on a persistent pool.
  */
 #include <math.h>
 #include <pthread.h>
@@ -46,40 +46,90 @@ typedef struct oracle_hparams { /* same layout as accel_hparams */
 
 /* ---- a pass = one statement over [0, count), split across threads -------- */
 typedef void (*pass_fn)(void *ctx, uint64_t lo, uint64_t hi, int tid);
-typedef struct {
+/* A persistent pool, as TF's intra-op thread pool is: workers are created once and park on a
+ * condition variable between passes (creating and joining threads for each of the 9 passes of a
+ * step would handicap this baseline). The calling thread works too (range 0). One pass at a
+ * time: callers are serialised by g_call. */
+#define POOL_MAX 256
+static struct {
+  pthread_mutex_t mu;
+  pthread_cond_t start, done;
+  pthread_t th[POOL_MAX];
+  int n_workers;          /* threads created so far (worker t handles range t + 1) */
+  unsigned long gen;      /* bumped once per pass */
+  int pending;            /* workers that have not finished the current pass */
   pass_fn fn;
   void *ctx;
-  uint64_t lo, hi;
-  int tid;
-} pass_job;
+  uint64_t count, per;
+  int ranges;             /* ranges of the current pass, range 0 is the caller's */
+} g_pool = {PTHREAD_MUTEX_INITIALIZER, PTHREAD_COND_INITIALIZER, PTHREAD_COND_INITIALIZER,
+            {0}, 0, 0, 0, NULL, NULL, 0, 0, 0};
+static pthread_mutex_t g_call = PTHREAD_MUTEX_INITIALIZER;
 
-static void *pass_thread(void *p) {
-  pass_job *j = (pass_job *)p;
-  j->fn(j->ctx, j->lo, j->hi, j->tid);
+static void run_range(pass_fn fn, void *ctx, uint64_t count, uint64_t per, int r) {
+  uint64_t lo = per * (uint64_t)r, hi = lo + per;
+  if (lo >= count) return;
+  if (hi > count) hi = count;
+  fn(ctx, lo, hi, r);
+}
+
+static void *pool_worker(void *p) {
+  const int r = (int)(intptr_t)p;   /* this worker's range index, >= 1 */
+  unsigned long seen = 0;
+  pthread_mutex_lock(&g_pool.mu);
+  for (;;) {
+    while (g_pool.gen == seen) pthread_cond_wait(&g_pool.start, &g_pool.mu);
+    seen = g_pool.gen;
+    const pass_fn fn = g_pool.fn;
+    void *ctx = g_pool.ctx;
+    const uint64_t count = g_pool.count, per = g_pool.per;
+    const int mine = r < g_pool.ranges;
+    pthread_mutex_unlock(&g_pool.mu);
+    if (mine) run_range(fn, ctx, count, per, r);
+    pthread_mutex_lock(&g_pool.mu);
+    if (--g_pool.pending == 0) pthread_cond_signal(&g_pool.done);
+  }
   return NULL;
 }
 
 static void run_pass(pass_fn fn, void *ctx, uint64_t count, int threads) {
   if (threads < 1) threads = 1;
-  if (threads > 256) threads = 256;
+  if (threads > POOL_MAX) threads = POOL_MAX;
   if (threads == 1 || count < 4096) {
     fn(ctx, 0, count, 0);
     return;
   }
-  pthread_t th[256];
-  pass_job job[256];
   /* ranges on 16-element boundaries so vector loops stay aligned */
-  uint64_t per = ((count + threads - 1) / threads + 15) & ~(uint64_t)15;
-  int started = 0;
-  for (int t = 0; t < threads; ++t) {
-    uint64_t lo = per * t, hi = lo + per;
-    if (lo >= count) break;
-    if (hi > count) hi = count;
-    job[t] = (pass_job){fn, ctx, lo, hi, t};
-    pthread_create(&th[t], NULL, pass_thread, &job[t]);
-    started = t + 1;
+  const uint64_t per = ((count + threads - 1) / threads + 15) & ~(uint64_t)15;
+  pthread_mutex_lock(&g_call);
+  pthread_mutex_lock(&g_pool.mu);
+  while (g_pool.n_workers < threads - 1) {   /* grow the pool on first use */
+    const int r = g_pool.n_workers + 1;
+    if (pthread_create(&g_pool.th[g_pool.n_workers], NULL, pool_worker, (void *)(intptr_t)r))
+      break;
+    pthread_detach(g_pool.th[g_pool.n_workers]);
+    ++g_pool.n_workers;
   }
-  for (int t = 0; t < started; ++t) pthread_join(th[t], NULL);
+  int ranges = g_pool.n_workers + 1;
+  if (ranges > threads) ranges = threads;
+  /* if thread creation fell short, the ranges that have no worker are run by the caller */
+  const uint64_t per_eff = ranges == threads
+                               ? per
+                               : ((count + ranges - 1) / ranges + 15) & ~(uint64_t)15;
+  g_pool.fn = fn;
+  g_pool.ctx = ctx;
+  g_pool.count = count;
+  g_pool.per = per_eff;
+  g_pool.ranges = ranges;
+  g_pool.pending = g_pool.n_workers;
+  ++g_pool.gen;
+  pthread_cond_broadcast(&g_pool.start);
+  pthread_mutex_unlock(&g_pool.mu);
+  run_range(fn, ctx, count, per_eff, 0);
+  pthread_mutex_lock(&g_pool.mu);
+  while (g_pool.pending != 0) pthread_cond_wait(&g_pool.done, &g_pool.mu);
+  pthread_mutex_unlock(&g_pool.mu);
+  pthread_mutex_unlock(&g_call);
 }
 
 /* ---- aggregation: ConditionalAccumulator ---------------------------------- */

@@ -165,12 +165,27 @@ def build_c_oracle(force: bool = False) -> str:
     return lib
 
 
+def build_native_c_oracle() -> str | None:
+    """The same source built -march=native ON THIS MACHINE (always rebuilt: a copy built on
+    another CPU could hold instructions this one lacks). Used by bench.py's timed CPU baseline
+    only; results are identical to the portable build (-ffp-contract=off in both)."""
+    lib = os.path.join(HERE, "liboracle_ps_native.so")
+    p = subprocess.run(["make", "-C", HERE, "-B", "liboracle_ps_native.so"], capture_output=True)
+    return lib if p.returncode == 0 and os.path.exists(lib) else None
+
+
 class COracle:
-    def __init__(self, threads: int | None = None):
-        path = build_c_oracle()
+    def __init__(self, threads: int | None = None, native: bool = False):
+        self.build = "x86-64-v3"
+        path = build_native_c_oracle() if native else None
+        if path:
+            self.build = "native"
+        else:
+            path = build_c_oracle()
         try:
             self.lib = ctypes.CDLL(path)
         except OSError:
+            self.build = "x86-64-v3"
             self.lib = ctypes.CDLL(build_c_oracle(force=True))
         self.threads = threads or (os.cpu_count() or 1)
         L = self.lib

@@ -25,7 +25,7 @@ def test_library_exports_every_declared_symbol(lib):
 
 
 def test_version(pkg):
-    assert pkg.accel.version() == 10100
+    assert pkg.accel.version() == 10200
 
 
 def test_hparams_layout_matches_header(pkg):

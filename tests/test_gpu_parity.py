@@ -448,3 +448,34 @@ def test_recorded_step_replays_correctly(pkg):
     torch.cuda.synchronize()
     assert np.array_equal(ps.var[:n].cpu().numpy(), var)
     assert ps.device_global_step() == 8
+
+
+def test_device_state_advances_once_per_step_with_many_variables(pkg, ctx):
+    """A task that applies its variables ONE BY ONE (round-robin buckets) must run TF's finish
+    step once per step, not once per variable: accel_apply_dev_state_ex(advance=0) on each
+    variable, then accel_opt_state_advance. Result = the flat-arena step, bit for bit."""
+    sizes = [4096, 24, 70_000]
+    n = sum(sizes)
+    rng = np.random.default_rng(9)
+    var = rng.standard_normal(n).astype(F)
+    m, v = np.zeros(n, F), np.zeros(n, F)
+    d_var, d_m, d_v = _to_dev(var), _to_dev(m), _to_dev(v)
+    hp = pkg.HParams(lr=0.01)
+    ohp = O.HParams(lr=0.01)
+    state = torch.zeros(4, dtype=torch.float32, device=DEV)
+    ctx.opt_state_init(state, hp, 0)
+    offs = np.cumsum([0] + sizes)
+    for step in range(4):
+        g = [(0.01 * rng.standard_normal(n)).astype(F) for _ in range(2)]
+        dg = [_to_dev(x) for x in g]
+        for k, sz in enumerate(sizes):
+            lo = int(offs[k])
+            ctx.apply_dev_state_ex(pkg.OPT_ADAM, d_var[lo:lo + sz], d_m[lo:lo + sz], d_v[lo:lo + sz],
+                                   [x[lo:lo + sz] for x in dg], hp, state, advance=False)
+        ctx.opt_state_advance(state, hp, True)
+        O.numpy_ps_step(O.ADAM, var, m, v, g, ohp)
+        ohp.advance()
+    assert np.array_equal(d_var.cpu().numpy(), var)
+    assert int(state[2:4].view(torch.int64).item()) == 4
+    b = state[:2].cpu().numpy()
+    assert b[0] == F(ohp.beta1_power) and b[1] == F(ohp.beta2_power)

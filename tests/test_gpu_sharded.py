@@ -33,7 +33,8 @@ def _oracle_hier(grads_per_rank, mean):
 
 @pytest.mark.parametrize("world,chunks", [(1, 1), (2, 1), (2, 3), (4, 4), (8, 1), (8, 5)])
 @pytest.mark.parametrize("opt", [O.SGD, O.MOMENTUM, O.ADAM])
-@pytest.mark.parametrize("workers,bf16,mean", [(1, False, False), (8, False, True), (3, True, True)])
+@pytest.mark.parametrize("workers,bf16,mean", [(1, False, False), (8, False, True), (3, True, True),
+                                               (1, True, False)])   # last: raw-bf16 stage slots
 def test_sharded_step_matches_oracle(pkg, world, chunks, opt, workers, bf16, mean):
     from kubeflow_controller_b200 import sharded
     elems = 100_003
@@ -142,11 +143,14 @@ def test_single_rank_pipelined_step_call(pkg):
 
 @pytest.mark.parametrize("world,slices", [(1, 1), (2, 1), (2, 4), (4, 7), (8, 16), (8, 64)])
 @pytest.mark.parametrize("opt", [O.SGD, O.MOMENTUM, O.ADAM])
-@pytest.mark.parametrize("workers,bf16,mean", [(1, False, False), (8, False, True), (5, True, True)])
-@pytest.mark.parametrize("overlap", [0, 1])
+@pytest.mark.parametrize("workers,bf16,mean", [(1, False, False), (8, False, True), (5, True, True),
+                                               (1, True, True)])    # last: raw-bf16 stage slots
+@pytest.mark.parametrize("overlap", [0, 1, 2])
 def test_one_kernel_step_matches_oracle(pkg, world, slices, opt, workers, bf16, mean, overlap):
     """The ONE-kernel step (push, apply, pull and closing wait overlapped inside a cooperative
-    launch), all ranks played by one launch on this GPU: bit-exact against the oracle."""
+    launch), all ranks played by one launch on this GPU: bit-exact against the oracle.
+    overlap 2 = the in-switch protocol (summers / reducers) in its peer-load form: a single
+    GPU has no NVSwitch, so the reduce is `world` loads in rank order — same bits."""
     from kubeflow_controller_b200 import sharded
     elems = 100_003
     agg = pkg.AGG_MEAN if mean else pkg.AGG_SUM
@@ -257,3 +261,115 @@ def test_sharded_global_norm_clip(pkg):
                   O.HParams(lr=0.1, momentum=0.9))
     for x in ranks:     # with the SAME sum of squares the rest is bit-exact
         assert np.array_equal(x.var.cpu().numpy(), var)
+
+
+def test_raw_bf16_stage_is_what_travels(pkg):
+    """One bf16 gradient per rank: the stage slots hold the raw bf16 items (2 B/elem), and the
+    result equals the fp32-slot path bit for bit."""
+    from kubeflow_controller_b200 import sharded
+    world, elems = 4, 50_000
+    rng = np.random.default_rng(11)
+    outs = []
+    for b16 in (True, False):
+        ranks = sharded.local_group(world, elems, pkg.OPT_ADAM, lambda: pkg.HParams(lr=0.01),
+                                    bf16_stage=b16)
+        padded, shard = ranks[0].padded, ranks[0].shard
+        rng = np.random.default_rng(11)
+        var = rng.standard_normal(padded).astype(F)
+        for x in ranks:
+            x.var.copy_(_dev(var))
+        gpr = [[O.f32_to_bf16_bits((0.01 * rng.standard_normal(padded)).astype(F))]
+               for _ in range(world)]
+        sharded.local_group_step(ranks, [[_dev(g) for g in gr] for gr in gpr])
+        if b16:
+            # slot s of rank r = rank s's gradient for shard r, as bf16, packed `shard` apart
+            r = 1
+            raw = ranks[r].stage.view(torch.int16).cpu().numpy().view(np.uint16)
+            for s_ in range(world):
+                assert np.array_equal(raw[s_ * shard:(s_ + 1) * shard],
+                                      gpr[s_][0][r * shard:(r + 1) * shard])
+        outs.append(ranks[0].var.cpu().numpy())
+    assert np.array_equal(outs[0], outs[1])
+
+
+def test_reset_after_timeout(pkg):
+    """After a provoked timeout the flag block is unusable until accel_shard_reset; after the
+    reset (every rank) the next step succeeds and is correct."""
+    from kubeflow_controller_b200 import sharded
+    ranks = sharded.local_group(2, 4096, pkg.OPT_SGD, lambda: pkg.HParams(lr=1.0))
+    ones = [[torch.ones(ranks[0].padded, device=DEV)] for _ in ranks]
+    ranks[0].push(ones[0])
+    ranks[0].apply_pull(2)                      # rank 1 never pushed
+    with pytest.raises(pkg.AccelError, match="timed out"):
+        ranks[0].check()
+    with pytest.raises(pkg.AccelError, match="timed out"):
+        ranks[0].check()                        # sticky until reset
+    for x in ranks:
+        x.reset()
+    sharded.local_group_step(ranks, ones)
+    sharded.local_group_step_fused(ranks, ones, n_slices=2)
+    for x in ranks:
+        assert torch.all(x.var == -4.0)
+
+
+def test_one_kernel_timeout_leaves_tickets_clean(pkg):
+    """A one-kernel step in which a rank never shows up times out, and afterwards every ticket
+    word is back at zero (all CTAs reach the closing ticket even when their waits failed)."""
+    from kubeflow_controller_b200 import sharded
+    ranks = sharded.local_group(2, 40_000, pkg.OPT_SGD, lambda: pkg.HParams(lr=1.0))
+    x = ranks[0]
+    g = [torch.ones(x.padded, device=DEV)]
+    # rank 0 alone runs the real one-kernel entry point against a peer that never launches
+    pkg.accel.check(x.lib.accel_shard_step_fused(
+        x.ctx.handle, __import__("ctypes").byref(x.peers), x.optimizer, None, None,
+        pkg.accel._grad_array(g), 1, pkg.F32, 2, __import__("ctypes").byref(x.hp), None, 2, 0,
+        pkg.accel._stream_handle(None)))
+    with pytest.raises(pkg.AccelError, match="timed out"):
+        x.check()
+    words = x.flags.cpu().numpy()
+    assert words[32] == 0 and words[33] == 0 and not words[64:128].any(), "tickets not released"
+    for r in ranks:
+        r.reset()
+    ones = [[torch.ones(x.padded, device=DEV)] for _ in ranks]
+    sharded.local_group_step_fused(ranks, ones, n_slices=2, overlap=2)
+    assert torch.all(ranks[1].var[ranks[1].shard:] == -2.0)
+
+
+@pytest.mark.parametrize("opt,bf16,workers,slices", [(O.SGD, False, 3, 1), (O.ADAM, False, 2, 5),
+                                                     (O.MOMENTUM, True, 1, 4), (O.ADAM, True, 2, 16)])
+def test_shard_step_host_world_of_one(pkg, opt, bf16, workers, slices):
+    """accel_shard_step_host (pinned host gradients -> sliced H2D -> push/apply_pull -> D2H of
+    the replica) with a world of one: the whole pipeline, no peer to wait for."""
+    from kubeflow_controller_b200 import sharded
+    n = 300_007
+    x = sharded.local_group(1, n, opt, lambda: pkg.HParams(lr=0.01, momentum=0.9))[0]
+    rng = np.random.default_rng(5)
+    var = rng.standard_normal(x.padded).astype(F)
+    s0, s1 = np.zeros(x.padded, F), np.zeros(x.padded, F)
+    x.var.copy_(_dev(var))
+    ohp = O.HParams(lr=0.01, momentum=0.9)
+    out = torch.empty(x.padded, dtype=torch.float32).pin_memory()
+    for _ in range(3):
+        g = [(0.01 * rng.standard_normal(x.padded)).astype(F) for _ in range(workers)]
+        if bf16:
+            g = [O.f32_to_bf16_bits(a) for a in g]
+            hg = [torch.from_numpy(a.view(np.int16)).view(torch.bfloat16).pin_memory() for a in g]
+        else:
+            hg = [torch.from_numpy(a).pin_memory() for a in g]
+        x.step_host(hg, out, n_slices=slices)
+        O.numpy_apply(opt, var, s0, s1, O.numpy_aggregate(g, False), ohp)
+        ohp.advance()
+        assert np.array_equal(out.numpy(), var), "host copy of the replica differs"
+    assert np.array_equal(x.var.cpu().numpy(), var)
+    with pytest.raises(pkg.AccelError, match="clip"):
+        x.hp.clip_norm = 1.0
+        x.step_host(hg, out)
+
+
+def test_rank_runs_on_the_device_it_was_given(pkg):
+    """ShardedPS(rank=1, device_index=0): the default context must map task 1 to GPU 0 (local
+    rank != rank on multi-node jobs), not to GPU 1."""
+    from kubeflow_controller_b200 import sharded
+    x = sharded.ShardedPS(1, 2, 0, 4096, pkg.OPT_SGD, pkg.HParams(lr=1.0),
+                          peer_ptrs=[(0, 0, 0, 0)] * 2)
+    assert x.ctx.gpu_of(1) == 0
