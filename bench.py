@@ -476,6 +476,19 @@ def sharded_configs(torch, dist, pkg, ShardedPS, rank, world, local, dev, stream
     for mode in modes:
         add(f"cfg3 ResNet-50-shaped (25.6M fp32) Momentum, {world} PS shards", RESNET50_ELEMS,
             pkg.OPT_MOMENTUM, False, dict(lr=0.1, momentum=0.9), mode, 1 if mode != "switch" else 2)
+    # the same model placed the reference's way (variable k -> PS task k mod P, buckets padded to
+    # equal length): same kernels, a larger and unbalanced arena
+    try:
+        import numpy as np
+        from kubeflow_controller_b200.sharded import BucketLayout
+        with open(os.path.join(ROOT, "tests", "golden", "model_shapes.json")) as f:
+            sizes = [int(np.prod(sh)) if sh else 1 for _, sh in json.load(f)["resnet50"]]
+        lay = BucketLayout(sizes, world)
+        add(f"cfg3 ResNet-50-shaped, round-robin-by-variable buckets (arena {lay.arena} = "
+            f"{lay.arena / sum(sizes):.3f} x flat), Momentum, {world} PS shards", lay.arena,
+            pkg.OPT_MOMENTUM, False, dict(lr=0.1, momentum=0.9), "fused", 1)
+    except Exception as e:   # noqa: BLE001
+        rows.append({"workload": "cfg3 round-robin buckets", "error": f"{type(e).__name__}: {e}"[:300]})
     # config 4: BERT-large-shaped, bf16 gradients -> fp32 Adam (named for 8 shards; run at any N)
     for mode, pull in (("fused", "f32"), ("switch", "f32"), ("fused", "bf16"), ("nccl", "f32")):
         add(f"cfg4 BERT-large-shaped (335M) bf16 grads -> fp32 Adam, {world} PS shards",

@@ -316,6 +316,18 @@ int accel_tfjob_action(int worker_replicas, int ps_replicas, int succeeded_worke
  * spec order. Returns 1 / 0, or a negative status. */
 int accel_tfjob_is_local_job(const int *replica_types, int n);
 
+/* LocalJob.Action (pkg/tensorflow/local.go:50-74) for a job whose first spec has type
+ * first_spec_type, with NewLocalJob's pod selection (:34-48: the pod is kept only when there is
+ * exactly one active pod) and compose()/labels() (:78-90) when a worker must be added: the new
+ * RuntimeID is `suffix` (5 characters, as generateRuntimeID draws them) and the template labels
+ * become {kubeflow.caicloud.io, job_type, runtime_id, tf_job_name}. *out_event receives the
+ * single event; *composed 1 when compose() ran; buf receives "runtime_id<TAB><id>\n" and then
+ * the template's labels as "key=value\n" lines sorted by key (none unless compose() ran).
+ * Returns bytes written excluding the NUL, or a negative status. */
+int accel_tfjob_local_action(const char *job_name, const char *runtime_id_in, int first_spec_type,
+                             int active_pods, int succeeded, const char *suffix,
+                             accel_event *out_event, int *composed, char *buf, size_t buflen);
+
 /* One whole sync of a distributed TFJob, as manageTFJob runs it
  * (pkg/controller/controller.go:369-425): NewDistributedJob, Action(), then the
  * events in list order — GetService(type, i) per service, GetSpec(type, i) per

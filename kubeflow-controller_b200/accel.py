@@ -32,7 +32,8 @@ SYMBOLS = [
     "accel_opt_state_init", "accel_opt_state_advance", "accel_apply_dev_state",
     "accel_apply_dev_state_ex",
     "accel_grad_sumsq", "accel_grad_sumsq_static", "accel_ps_step_host", "accel_host_register", "accel_host_unregister",
-    "accel_tfjob_action", "accel_tfjob_is_local_job", "accel_tfjob_sync_plan",
+    "accel_tfjob_action", "accel_tfjob_is_local_job", "accel_tfjob_local_action",
+    "accel_tfjob_sync_plan",
     "accel_tfjob_service_key", "accel_tfjob_cluster_spec",
     "accel_tfjob_labels", "accel_tfjob_parse_argv", "accel_ipc_export", "accel_ipc_open",
     "accel_ipc_close", "accel_dev_alloc", "accel_dev_free", "accel_shard_push",
@@ -154,6 +155,9 @@ def load_library() -> ctypes.CDLL:
     L.accel_tfjob_sync_plan.argtypes = [ctypes.c_char_p, ctypes.c_char_p] + [i32] * 7 + \
         [ctypes.POINTER(ctypes.c_char_p), i32, ctypes.c_char_p, ctypes.c_size_t]
     L.accel_tfjob_is_local_job.argtypes = [ctypes.POINTER(i32), i32]
+    L.accel_tfjob_local_action.argtypes = [ctypes.c_char_p, ctypes.c_char_p, i32, i32, i32,
+                                           ctypes.c_char_p, ctypes.POINTER(Event),
+                                           ctypes.POINTER(i32), ctypes.c_char_p, ctypes.c_size_t]
     L.accel_shard_step.argtypes = [vp, ctypes.POINTER(Peers), i32, vp, vp, pvp, i32, i32, i32, php,
                                    vp, i32, vp]
     L.accel_shard_step_fused.argtypes = [vp, ctypes.POINTER(Peers), i32, vp, vp, pvp, i32, i32, i32,

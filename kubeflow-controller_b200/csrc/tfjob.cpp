@@ -184,6 +184,33 @@ bool IsLocalJob(const TFJob &job) {
   return !job.specs.empty() && job.specs[0].type == ReplicaType::Local;
 }
 
+LocalJob::LocalJob(TFJob *job, int active_pods, int succeeded, SuffixSource *names)
+    : job_(job), has_pod_(active_pods == 1), succeeded_(succeeded), names_(names) {}
+
+Event LocalJob::Action() {
+  // had a succeeded result: no new pod
+  if (succeeded_ > 0) return {ActionType::Nothing, 0};
+  const int active = has_pod_ ? 1 : 0;
+  if (active < kExpectedLocalWorkerNumber) {
+    compose();
+    return {ActionType::ShouldAddWorker, kExpectedLocalWorkerNumber - active};
+  }
+  return {ActionType::Nothing, 0};
+}
+
+void LocalJob::compose() {
+  job_->runtime_id = generate_name("", *names_);  // generateRuntimeID
+  spec_of(job_, 0).template_labels = labels();
+  composed_ = true;
+}
+
+std::map<std::string, std::string> LocalJob::labels() const {
+  return {{"kubeflow.caicloud.io", "true"},
+          {"job_type", replica_type_name(job_->specs[0].type)},
+          {"runtime_id", job_->runtime_id},
+          {"tf_job_name", job_->name}};
+}
+
 static std::vector<std::string> split_commas(const std::string &s) {
   std::vector<std::string> out;
   size_t start = 0;
@@ -313,6 +340,38 @@ int accel_tfjob_is_local_job(const int *replica_types, int n) {
     job.specs.push_back({1, t, {}, {}});
   }
   return tfjob::IsLocalJob(job) ? 1 : 0;
+}
+
+int accel_tfjob_local_action(const char *job_name, const char *runtime_id_in, int first_spec_type,
+                             int active_pods, int succeeded, const char *suffix,
+                             accel_event *out_event, int *composed, char *buf, size_t buflen) {
+  if (!job_name || !runtime_id_in || !out_event)
+    return fail(ACCEL_ERR_INVALID, "job_name/runtime_id_in/out_event is NULL");
+  if (active_pods < 0 || succeeded < 0)
+    return fail(ACCEL_ERR_INVALID, "active_pods/succeeded must be >= 0");
+  tfjob::ReplicaType t;
+  if (first_spec_type == ACCEL_REPLICA_LOCAL) {
+    t = tfjob::ReplicaType::Local;
+  } else if (!to_type(first_spec_type, &t)) {
+    return fail(ACCEL_ERR_INVALID, "unknown replica_type %d", first_spec_type);
+  }
+  tfjob::TFJob job;
+  job.name = job_name;
+  job.runtime_id = runtime_id_in;
+  job.specs.push_back({1, t, {}, {}});
+  try {
+    tfjob::FixedSuffixSource names({suffix ? suffix : ""});
+    tfjob::LocalJob lj(&job, active_pods, succeeded, &names);
+    const tfjob::Event e = lj.Action();
+    out_event->action = static_cast<int32_t>(e.action);
+    out_event->number = e.number;
+    if (composed) *composed = lj.composed() ? 1 : 0;
+    std::string s = "runtime_id\t" + job.runtime_id + "\n";
+    for (const auto &kv : job.specs[0].template_labels) s += kv.first + "=" + kv.second + "\n";
+    return copy_out(s, buf, buflen);
+  } catch (const std::exception &ex) {
+    return fail(ACCEL_ERR_INVALID, "%s", ex.what());
+  }
 }
 
 int accel_tfjob_sync_plan(const char *job_name, const char *runtime_id_in, int worker_replicas,

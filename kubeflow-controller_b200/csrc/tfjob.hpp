@@ -126,6 +126,26 @@ class DistributedJob {
 // checker.IsLocalJob (pkg/checker/checker.go:8-14)
 bool IsLocalJob(const TFJob &job);
 
+// pkg/tensorflow/local.go: the single-replica job. NewLocalJob (:34-48) keeps the pod only when
+// there is exactly ONE active pod — with two or more it logs and keeps none, so Action then asks
+// for a new worker; that behaviour is kept. Action :50-74, compose :78-81, labels :83-90.
+constexpr int kExpectedLocalWorkerNumber = 1;   // local.go:22-24
+class LocalJob {
+ public:
+  LocalJob(TFJob *job, int active_pods, int succeeded, SuffixSource *names);
+  Event Action();
+  std::map<std::string, std::string> labels() const;
+  bool composed() const { return composed_; }
+
+ private:
+  void compose();
+  TFJob *job_;
+  bool has_pod_;
+  int succeeded_;
+  SuffixSource *names_;
+  bool composed_ = false;
+};
+
 // The cluster a replica sees after parsing its four flags
 // (examples/workdir/mnist_replica.py:107-115).
 struct ClusterView {

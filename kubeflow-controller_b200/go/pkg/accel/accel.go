@@ -74,6 +74,16 @@ func status(rc C.int) error {
 	return fmt.Errorf("accel: status %d: %s", int(rc), C.GoString(C.accel_last_error()))
 }
 
+// locked runs ONE C call and, if it failed, reads its message — both on the same OS thread.
+// accel_last_error() is thread-local in the library and goroutines migrate between OS threads
+// from one cgo call to the next, so the call and the fetch must not be separated. The library
+// also sets the CUDA device per call (task -> GPU), which is per-thread state as well.
+func locked(f func() C.int) error {
+	runtime.LockOSThread()
+	defer runtime.UnlockOSThread()
+	return status(f())
+}
+
 // Context maps PS task_index -> GPU ordinal and owns per-GPU scratch.
 type Context struct{ h *C.accel_ctx }
 
@@ -92,7 +102,7 @@ func NewContext(nPS int, gpuOrdinals []int) (*Context, error) {
 		p = &arr[0]
 	}
 	c := &Context{}
-	if err := status(C.accel_ctx_create(p, C.int(nPS), &c.h)); err != nil {
+	if err := locked(func() C.int { return C.accel_ctx_create(p, C.int(nPS), &c.h) }); err != nil {
 		return nil, err
 	}
 	runtime.SetFinalizer(c, func(c *Context) { c.Close() })
@@ -116,8 +126,13 @@ func (c *Context) GPUOf(task int) (int, error) {
 // DevPtr is a caller-owned device address (from the process's CUDA allocator).
 type DevPtr uintptr
 
+// gradArray copies the pointers into C memory. With no gradients it returns nil (the library
+// then rejects the call with ACCEL_ERR_INVALID) instead of indexing an empty allocation.
 func gradArray(grads []DevPtr) (*unsafe.Pointer, func()) {
 	n := len(grads)
+	if n == 0 {
+		return nil, func() {}
+	}
 	mem := (*[1 << 20]unsafe.Pointer)(C.malloc(C.size_t(n) * C.size_t(unsafe.Sizeof(uintptr(0)))))
 	for i, g := range grads {
 		mem[i] = unsafe.Pointer(uintptr(g))
@@ -131,9 +146,9 @@ func (c *Context) ApplySGD(task int, v DevPtr, grads []DevPtr, dt DType, count u
 	g, free := gradArray(grads)
 	defer free()
 	ch := hp.c()
-	return status(C.accel_apply_sgd(c.h, C.int(task), (*C.float)(unsafe.Pointer(uintptr(v))), g,
+	return locked(func() C.int { return C.accel_apply_sgd(c.h, C.int(task), (*C.float)(unsafe.Pointer(uintptr(v))), g,
 		C.int(len(grads)), C.int(dt), C.uint64_t(count), &ch,
-		(*C.float)(unsafe.Pointer(uintptr(sumsq))), C.accel_stream_t(unsafe.Pointer(stream))))
+		(*C.float)(unsafe.Pointer(uintptr(sumsq))), C.accel_stream_t(unsafe.Pointer(stream))) })
 }
 
 // ApplyMomentum: accum = accum*momentum + G; var -= accum*lr (or the Nesterov form).
@@ -142,10 +157,10 @@ func (c *Context) ApplyMomentum(task int, v, accum DevPtr, grads []DevPtr, dt DT
 	g, free := gradArray(grads)
 	defer free()
 	ch := hp.c()
-	return status(C.accel_apply_momentum(c.h, C.int(task),
+	return locked(func() C.int { return C.accel_apply_momentum(c.h, C.int(task),
 		(*C.float)(unsafe.Pointer(uintptr(v))), (*C.float)(unsafe.Pointer(uintptr(accum))), g,
 		C.int(len(grads)), C.int(dt), C.uint64_t(count), &ch,
-		(*C.float)(unsafe.Pointer(uintptr(sumsq))), C.accel_stream_t(unsafe.Pointer(stream))))
+		(*C.float)(unsafe.Pointer(uintptr(sumsq))), C.accel_stream_t(unsafe.Pointer(stream))) })
 }
 
 // ApplyAdam: TF-1.4 ApplyAdam on the aggregated gradient; call hp.AdvanceAdam() after
@@ -155,10 +170,10 @@ func (c *Context) ApplyAdam(task int, v, m, vv DevPtr, grads []DevPtr, dt DType,
 	g, free := gradArray(grads)
 	defer free()
 	ch := hp.c()
-	return status(C.accel_apply_adam(c.h, C.int(task), (*C.float)(unsafe.Pointer(uintptr(v))),
+	return locked(func() C.int { return C.accel_apply_adam(c.h, C.int(task), (*C.float)(unsafe.Pointer(uintptr(v))),
 		(*C.float)(unsafe.Pointer(uintptr(m))), (*C.float)(unsafe.Pointer(uintptr(vv))), g,
 		C.int(len(grads)), C.int(dt), C.uint64_t(count), &ch,
-		(*C.float)(unsafe.Pointer(uintptr(sumsq))), C.accel_stream_t(unsafe.Pointer(stream))))
+		(*C.float)(unsafe.Pointer(uintptr(sumsq))), C.accel_stream_t(unsafe.Pointer(stream))) })
 }
 
 // GradSumSq writes sum(aggregate(grads)^2) to the device scalar `out`.
@@ -166,9 +181,9 @@ func (c *Context) GradSumSq(task int, grads []DevPtr, dt DType, count uint64, ag
 	out DevPtr, stream uintptr) error {
 	g, free := gradArray(grads)
 	defer free()
-	return status(C.accel_grad_sumsq(c.h, C.int(task), g, C.int(len(grads)), C.int(dt),
+	return locked(func() C.int { return C.accel_grad_sumsq(c.h, C.int(task), g, C.int(len(grads)), C.int(dt),
 		C.uint64_t(count), C.int(agg), (*C.float)(unsafe.Pointer(uintptr(out))),
-		C.accel_stream_t(unsafe.Pointer(stream))))
+		C.accel_stream_t(unsafe.Pointer(stream))) })
 }
 
 // StepHost runs one PS step with the workers' gradients in (page-locked) host memory and
@@ -182,8 +197,8 @@ func (c *Context) StepHost(task int, optimizer int, v, slot0, slot1 DevPtr,
 	g, free := gradArray(ptrs)
 	defer free()
 	ch := hp.c()
-	return status(C.accel_ps_step_host(c.h, C.int(task), C.int(optimizer),
+	return locked(func() C.int { return C.accel_ps_step_host(c.h, C.int(task), C.int(optimizer),
 		(*C.float)(unsafe.Pointer(uintptr(v))), (*C.float)(unsafe.Pointer(uintptr(slot0))),
 		(*C.float)(unsafe.Pointer(uintptr(slot1))), g, C.int(len(hostGrads)), C.int(dt),
-		C.uint64_t(count), &ch, (*C.float)(hostVarOut)))
+		C.uint64_t(count), &ch, (*C.float)(hostVarOut)) })
 }

@@ -37,8 +37,8 @@ type Shard struct{ Offset, Count uint64 }
 func PlanFlat(nElems uint64, nPS int, alignElems uint64) ([]Shard, uint64, error) {
 	out := make([]C.accel_shard, nPS)
 	var padded C.uint64_t
-	if err := status(C.accel_plan_flat(C.uint64_t(nElems), C.int(nPS), C.uint64_t(alignElems),
-		&out[0], &padded)); err != nil {
+	if err := locked(func() C.int { return C.accel_plan_flat(C.uint64_t(nElems), C.int(nPS), C.uint64_t(alignElems),
+		&out[0], &padded) }); err != nil {
 		return nil, 0, err
 	}
 	shards := make([]Shard, nPS)
@@ -63,8 +63,8 @@ func PlanRoundRobin(varElems []uint64, nPS, firstTask int, alignElems uint64) (t
 	ct := make([]C.int, n)
 	co := make([]C.uint64_t, n)
 	cb := make([]C.uint64_t, nPS)
-	if err = status(C.accel_plan_round_robin(&ve[0], C.int(n), C.int(nPS), C.int(firstTask),
-		C.uint64_t(alignElems), &ct[0], &co[0], &cb[0])); err != nil {
+	if err = locked(func() C.int { return C.accel_plan_round_robin(&ve[0], C.int(n), C.int(nPS), C.int(firstTask),
+		C.uint64_t(alignElems), &ct[0], &co[0], &cb[0]) }); err != nil {
 		return
 	}
 	task, offset, bucket = make([]int, n), make([]uint64, n), make([]uint64, nPS)

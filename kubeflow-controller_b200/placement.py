@@ -34,6 +34,26 @@ def is_local_job(replica_types) -> bool:
     return bool(accel.check(L.accel_tfjob_is_local_job(arr, len(replica_types))))
 
 
+def local_action(job: str, runtime_id: str, active_pods: int, succeeded: int, suffix: str = "",
+                 first_spec_type: str = "Local"):
+    """LocalJob.Action with NewLocalJob's pod selection and compose()/labels()
+    (pkg/tensorflow/local.go:34-90) -> ((action name, number), composed, runtime id after,
+    template labels after)."""
+    L = accel.load_library()
+    codes = {"PS": accel.REPLICA_PS, "Worker": accel.REPLICA_WORKER, "Local": accel.REPLICA_LOCAL}
+    ev = accel.Event()
+    composed = ctypes.c_int()
+    buf = ctypes.create_string_buffer(2048)
+    accel.check(L.accel_tfjob_local_action(job.encode(), runtime_id.encode(),
+                                           codes[first_spec_type], active_pods, succeeded,
+                                           suffix.encode(), ctypes.byref(ev),
+                                           ctypes.byref(composed), buf, len(buf)))
+    lines = buf.value.decode().splitlines()
+    rid = lines[0].split("\t", 1)[1] if "\t" in lines[0] else ""
+    labels_ = dict(ln.split("=", 1) for ln in lines[1:])
+    return (accel.ACTION_NAMES[ev.action], ev.number), bool(composed.value), rid, labels_
+
+
 def sync_plan(job: str, runtime_id: str, workers: int, ps: int, suffixes, succeeded=0,
               worker_services=0, ps_services=0, active_workers=0, active_ps=0):
     """One sync of manageTFJob (pkg/controller/controller.go:369-425) ->

@@ -81,6 +81,38 @@ def shard_layout(elems: int, world: int, align: int = 8):
     return padded, padded // world
 
 
+class BucketLayout:
+    """TF-faithful placement for the sharded step (SURVEY §8 e): variable k (creation order)
+    belongs to PS task k mod P (tf.train.replica_device_setter, the call site is
+    examples/workdir/mnist_replica.py:137-141); each task's variables are packed into bucket r
+    and the buckets are padded to ONE length, so bucket r is exactly shard r of the arena the
+    flat step works on — the kernels are the same, only the layout differs. Unlike the flat
+    plan the shards are as unbalanced as the round-robin makes them (arena = P x the largest
+    bucket)."""
+
+    def __init__(self, var_elems, world: int, first_task: int = 0, align: int = 8):
+        self.var_elems = list(var_elems)
+        self.world = world
+        self.task, self.offset, self.fill = accel.plan_round_robin(self.var_elems, world,
+                                                                   first_task, align)
+        self.shard = max(8, -(-max(self.fill) // 8) * 8)
+        self.arena = self.shard * world
+        self.pos = [t * self.shard + o for t, o in zip(self.task, self.offset)]
+
+    def view(self, arena, k: int):
+        """Variable k inside an arena-shaped tensor."""
+        return arena[self.pos[k]:self.pos[k] + self.var_elems[k]]
+
+    def pack(self, tensors, out=None):
+        """Per-variable tensors -> one arena-shaped tensor (padding zero)."""
+        import torch
+        if out is None:
+            out = torch.zeros(self.arena, dtype=tensors[0].dtype, device=tensors[0].device)
+        for k, t in enumerate(tensors):
+            self.view(out, k).copy_(t.reshape(-1))
+        return out
+
+
 def exchange(obj, world: int):
     """All-gather a picklable object over the job's rendezvous (gloo or nccl group)."""
     import torch.distributed as dist

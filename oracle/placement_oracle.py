@@ -54,6 +54,20 @@ def action(workers: int, ps: int, succeeded: int, worker_svcs: int, ps_svcs: int
     return ev, composed
 
 
+def local_action(job: str, runtime_id: str, active_pods: int, succeeded: int, suffix: str,
+                 first_spec_type: str = "Local"):
+    """LocalJob.Action (/root/reference/pkg/tensorflow/local.go:50-74) with NewLocalJob's pod
+    selection (:34-48 — a pod is kept only when exactly one is active) and compose()/labels()
+    (:78-90). -> ((action, number), composed, runtime id after, template labels after)."""
+    if succeeded > 0:
+        return ("Nothing", 0), False, runtime_id, {}
+    active = 1 if active_pods == 1 else 0
+    if active < 1:
+        rid = generate_name("", suffix)
+        return ("ShouldAddWorker", 1 - active), True, rid, labels(job, first_spec_type, rid)
+    return ("Nothing", 0), False, runtime_id, {}
+
+
 def cluster_spec(job: str, workers: int, ps: int, service_names: dict, typ: str, index: int):
     """generateTFClusterSpec (distributed.go:127-159). service_names: key -> generated
     name; a missing key reads as "" like a Go map."""

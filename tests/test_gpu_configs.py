@@ -164,3 +164,43 @@ def test_config5_size_sweep(pkg, mib, opt):
         delta = before - var.double().sum().item()
         want = 0.01 * g.double().sum().item()
         assert abs(delta - want) <= 1e-4 * max(1.0, abs(want)) + 1e-3 * (n / 1e8)
+
+
+@pytest.mark.parametrize("world", [2, 8])
+def test_config3_round_robin_buckets_through_the_sharded_step(pkg, world):
+    """Config 3 with the reference's placement INSIDE the multi-GPU step: variable k on PS task
+    k mod P (mnist_replica.py:137-141), buckets padded to equal length so bucket r = shard r,
+    one worker gradient per rank, the one-kernel step. Every variable must match the oracle
+    applied to that variable alone, and must live in the shard of rank k mod P."""
+    from kubeflow_controller_b200 import sharded
+    sizes = _sizes("resnet50")
+    lay = sharded.BucketLayout(sizes, world)
+    assert lay.arena == lay.shard * world and lay.shard >= max(lay.fill)
+    for k in range(len(sizes)):
+        assert lay.pos[k] // lay.shard == k % world
+        assert (lay.pos[k] + sizes[k] - 1) // lay.shard == k % world      # never straddles
+    ranks = sharded.local_group(world, lay.arena, pkg.OPT_MOMENTUM,
+                                lambda: pkg.HParams(lr=0.1, momentum=0.9))
+    assert ranks[0].padded == lay.arena and ranks[0].shard == lay.shard
+    rng = np.random.default_rng(8)
+    var = [rng.standard_normal(s).astype(F) for s in sizes]
+    acc = [np.zeros(s, F) for s in sizes]
+    arena = lay.pack([torch.from_numpy(v).to(DEV) for v in var])
+    for x in ranks:
+        x.var.copy_(arena)
+    for step in range(2):
+        per_rank = [[(0.01 * rng.standard_normal(s)).astype(F) for s in sizes]
+                    for _ in range(world)]
+        dg = [[lay.pack([torch.from_numpy(g).to(DEV) for g in gr])] for gr in per_rank]
+        sharded.local_group_step_fused(ranks, dg, n_slices=2)
+        for k in range(len(sizes)):
+            O.numpy_ps_step(O.MOMENTUM, var[k], acc[k], None, [gr[k] for gr in per_rank],
+                            O.HParams(lr=0.1, momentum=0.9))
+    for x in ranks:
+        for k in range(len(sizes)):
+            assert np.array_equal(lay.view(x.var, k).cpu().numpy(), var[k]), f"variable {k}"
+    # optimizer slots stay with the owner: variable k's accumulator is in rank (k mod P)'s slot0
+    for k in (0, 1, len(sizes) - 1):
+        owner = ranks[k % world]
+        got = owner.slot0[lay.offset[k]:lay.offset[k] + sizes[k]].cpu().numpy()
+        assert np.array_equal(got, acc[k])

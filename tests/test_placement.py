@@ -281,3 +281,26 @@ def test_sync_plan_errors(P, pkg):
         P.sync_plan("j", "", 2, 1, SFX[:2])          # needs 1 + 2 + 1 suffixes
     with pytest.raises(pkg.AccelError, match="5 characters"):
         P.sync_plan("j", "", 1, 1, ["abc", "bcdfg", "bcdfg"])
+
+
+# ---- LocalJob (pkg/tensorflow/local.go:34-90) ------------------------------------------------
+@pytest.mark.parametrize("active", [0, 1, 2, 3])
+@pytest.mark.parametrize("succeeded", [0, 1, 2])
+def test_local_action_matches_restatement(P, active, succeeded):
+    got = P.local_action("local-job", "oldid", active, succeeded, "bcdfg")
+    assert got == PO.local_action("local-job", "oldid", active, succeeded, "bcdfg")
+
+
+def test_local_action_quirks(P):
+    # no pod yet: one worker to add, a fresh RuntimeID, labels carry job_type "Local"
+    ev, composed, rid, lab = P.local_action("mnist", "", 0, 0, "x2456")
+    assert ev == ("ShouldAddWorker", 1) and composed and rid == "x2456"
+    assert lab == {"kubeflow.caicloud.io": "true", "job_type": "Local", "runtime_id": "x2456",
+                   "tf_job_name": "mnist"}
+    # one active pod: nothing to do, the stored RuntimeID stays
+    assert P.local_action("mnist", "keep5", 1, 0, "x2456") == (("Nothing", 0), False, "keep5", {})
+    # TWO active pods: NewLocalJob keeps none (local.go:41-43 only logs), so Action asks for one more
+    ev, composed, rid, _ = P.local_action("mnist", "keep5", 2, 0, "x2456")
+    assert ev == ("ShouldAddWorker", 1) and composed and rid == "x2456"
+    # a succeeded pod wins over everything
+    assert P.local_action("mnist", "keep5", 0, 1, "x2456")[0] == ("Nothing", 0)

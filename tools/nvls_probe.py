@@ -1,7 +1,15 @@
 #!/usr/bin/env python
-"""Raw rates of NVSwitch multicast stores / in-switch reductions (development probe; torchrun).
-Every rank works on its own shard of a symmetric buffer at the same time, as a fused step would."""
+"""Raw rates of the cross-GPU memory operations a fused step can use (development probe;
+torchrun, one process per GPU; tools/probe/libaccel_probe.so — not the product library).
+Every rank works on its own shard of a symmetric buffer at the same time, as a fused step would.
+
+  peer stores: 128-bit, 256-bit (what the step kernels issue) and bulk-async 4 KiB
+  (cp.async.bulk shared -> peer global); peer loads; multimem.st; multimem.ld_reduce; and the
+  in-switch steady state (ld_reduce of the own shard + multimem.st of the result, both link
+  directions busy).
+One JSON line per (operation, grid) on rank 0."""
 import ctypes
+import json
 import os
 import sys
 
@@ -10,8 +18,16 @@ import torch.distributed as dist
 
 ROOT = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
 sys.path.insert(0, ROOT)
-import kubeflow_controller_b200 as pkg  # noqa: E402
 from kubeflow_controller_b200.sharded import SymmBuffer  # noqa: E402
+
+MODES = [(2, "local copy (HBM reference)", "none"),
+         (3, "peer load 128-bit (right neighbour)", "uni"),
+         (4, "peer store 128-bit (right neighbour)", "uni"),
+         (5, "peer store 256-bit st.global.v8.f32 (right neighbour)", "uni"),
+         (6, "peer store bulk-async 4 KiB cp.async.bulk (right neighbour)", "uni"),
+         (0, "multimem.st own shard (all-gather pattern)", "mc"),
+         (1, "multimem.ld_reduce own shard (reduce-scatter pattern)", "mc"),
+         (7, "ld_reduce own shard + multimem.st of the result (in-switch steady state)", "mc")]
 
 
 def main():
@@ -20,28 +36,28 @@ def main():
     dev = torch.device("cuda", local)
     torch.cuda.set_device(dev)
     dist.init_process_group("nccl", device_id=dev)
-    lib = pkg.load_library()
-    fn = lib.accel_dev_probe_multimem
-    fn.argtypes = [ctypes.c_void_p, ctypes.c_void_p, ctypes.c_uint64, ctypes.c_uint64, ctypes.c_int,
-                   ctypes.c_int, ctypes.c_void_p]
+    lib = ctypes.CDLL(os.path.join(ROOT, "tools", "probe", "libaccel_probe.so"))
+    fn = lib.accel_probe_run
+    fn.argtypes = [ctypes.c_void_p, ctypes.c_void_p, ctypes.c_void_p, ctypes.c_uint64,
+                   ctypes.c_uint64, ctypes.c_int, ctypes.c_int, ctypes.c_void_p]
     fn.restype = ctypes.c_int
-    shard = 64 << 20                      # elements per rank (256 MB)
+    shard = int(os.environ.get("PROBE_SHARD_MIB", "256")) << 18     # elements per rank
     buf = SymmBuffer(shard * world * 4, local)
-    if not buf.multicast_ptr:
-        if rank == 0:
-            print("no multicast support on this fabric")
-        return
+    buf2 = SymmBuffer(shard * world * 4, local)
     loc = torch.randn(2 * shard, device=dev)
     stream = torch.cuda.current_stream()
     peer = buf.peer_ptrs[(rank + 1) % world]
-    for mode, name in ((2, "local copy"), (3, "peer load (right neighbour)"),
-                       (4, "peer store (right neighbour)"), (0, "multimem.st (all-gather)"),
-                       (1, "multimem.ld_reduce (reduce-scatter)")):
-        for ctas in (296, 592, 1184):
+    for mode, name, kind in MODES:
+        if kind == "mc" and not (buf.multicast_ptr and buf2.multicast_ptr):
+            if rank == 0:
+                print(json.dumps({"op": name, "skipped": "no multicast mapping on this fabric"}))
+            continue
+        for ctas in (148, 296, 592, 1184):
             def go():
-                base = peer if mode in (3, 4) else buf.multicast_ptr
-                pkg.accel.check(fn(base, loc.data_ptr(), rank * shard, shard, mode,
-                                   ctas, stream.cuda_stream))
+                base = peer if kind == "uni" else buf.multicast_ptr
+                rc = fn(base, loc.data_ptr(), buf2.multicast_ptr or None, rank * shard, shard, mode,
+                        ctas, stream.cuda_stream)
+                assert rc == 0, rc
             for _ in range(3):
                 go()
             torch.cuda.synchronize()
@@ -57,8 +73,12 @@ def main():
             dist.barrier()
             if rank == 0:
                 gb = shard * 4 / 1e9
-                print(f"{name:38s} ctas={ctas:5d} {t.item():.4f} ms  shard {gb / t.item() * 1e3:7.1f} GB/s"
-                      f"  (x{world - 1} fan = {gb * (world - 1) / t.item() * 1e3:7.1f} GB/s)", flush=True)
+                row = {"op": name, "world": world, "ctas": ctas, "shard_mb": round(gb * 1e3, 1),
+                       "ms": round(t.item(), 4), "shard_gbs": round(gb / t.item() * 1e3, 1)}
+                if kind == "mc":
+                    # per GPU: the switch moves `world` shards through one direction of its link
+                    row["link_gbs_busy_dir"] = round(gb * world / t.item() * 1e3, 1)
+                print(json.dumps(row), flush=True)
     dist.destroy_process_group()
 
 
