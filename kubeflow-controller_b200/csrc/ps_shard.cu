@@ -469,16 +469,12 @@ int accel_shard_step(accel_ctx *ctx, const accel_peers *peers, int optimizer, fl
   return do_wait_pull(ctx, peers, epoch, s);
 }
 
-// `rows` runs of `width` bytes, `pitch` bytes apart on both sides. One 2-D copy while the pitch
-// is within the runtime's limit for pitched copies, one 1-D copy per row beyond it.
+// `rows` runs of `width` bytes, `pitch` bytes apart on both sides: one 1-D copy per run (plain
+// DMA transfers of a few MB each; no pitch limit to respect for multi-GiB shards).
 static int copy_rows(void *dst, const void *src, size_t pitch, size_t width, int rows,
                      cudaMemcpyKind kind, cudaStream_t s) {
-  if (rows == 1 || width == pitch) {
-    ACCEL_CUDA(cudaMemcpyAsync(dst, src, width == pitch ? pitch * rows : width, kind, s));
-    return ACCEL_OK;
-  }
-  if (pitch < (size_t{1} << 30)) {
-    ACCEL_CUDA(cudaMemcpy2DAsync(dst, pitch, src, pitch, width, rows, kind, s));
+  if (width == pitch) {
+    ACCEL_CUDA(cudaMemcpyAsync(dst, src, pitch * rows, kind, s));
     return ACCEL_OK;
   }
   for (int r = 0; r < rows; ++r)

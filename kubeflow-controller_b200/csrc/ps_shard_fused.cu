@@ -22,8 +22,10 @@
 
 namespace accel {
 
+// One item per thread and iteration: the form for 4, 8 or a run-time number of gradients
+// (registers: 8 gradients x 8 values are already 64 in flight).
 template <typename G, int NW>
-__device__ __forceinline__ void push_slice(const ShardArgs &a, uint64_t sub_first,
+__device__ __forceinline__ void push_slice_one(const ShardArgs &a, uint64_t sub_first,
                                            uint64_t sub_items, int bid, int nb) {
   const uint64_t shard_items = a.shard / 8;
   const uint64_t granules = (sub_items + kPushGranule - 1) / kPushGranule;   // per owner
@@ -74,6 +76,89 @@ __device__ __forceinline__ void push_slice(const ShardArgs &a, uint64_t sub_firs
       }
     }
     st_256(a.stage[c] + (static_cast<uint64_t>(a.rank) * shard_items + within) * 8, acc);
+  }
+}
+
+template <typename G, int NW>
+__device__ __forceinline__ void push_slice(const ShardArgs &a, uint64_t sub_first,
+                                           uint64_t sub_items, int bid, int nb) {
+  // items in flight per thread: the 4- and 8-gradient forms already have that many loads
+  // outstanding; with one or two gradient streams a thread takes several items at once so that
+  // neither HBM latency nor the link's is exposed (matters most for small shards)
+  constexpr int U = (NW == 1) ? 4 : (NW == 2) ? 2 : 1;
+  if constexpr (U == 1) {
+    push_slice_one<G, NW>(a, sub_first, sub_items, bid, nb);
+    return;
+  }
+  const uint64_t shard_items = a.shard / 8;
+  const uint64_t granules = (sub_items + kPushGranule - 1) / kPushGranule;   // per owner
+  const uint64_t n_items = granules * kPushGranule * a.world;
+  const int n = NW > 0 ? NW : a.n_workers;
+  const uint64_t stride = static_cast<uint64_t>(nb) * blockDim.x;
+  for (uint64_t l0 = static_cast<uint64_t>(bid) * blockDim.x + threadIdx.x; l0 < n_items;
+       l0 += stride * U) {
+    uint64_t item[U], dst[U];
+    int owner[U];
+    bool ok[U];
+#pragma unroll
+    for (int j = 0; j < U; ++j) {
+      const uint64_t l = l0 + stride * j;
+      // granule g goes to owner (rank + 1 + g) mod world: all owners are written all the time
+      const uint64_t g_idx = l / kPushGranule;
+      const uint64_t in_shard = (g_idx / a.world) * kPushGranule + (l % kPushGranule);
+      ok[j] = l < n_items && in_shard < sub_items;
+      int c = a.rank + 1 + static_cast<int>(g_idx % a.world);
+      if (c >= a.world) c -= a.world;
+      owner[j] = ok[j] ? c : a.rank;
+      const uint64_t within = sub_first + (ok[j] ? in_shard : 0);
+      item[j] = static_cast<uint64_t>(owner[j]) * shard_items + within;
+      dst[j] = static_cast<uint64_t>(a.rank) * shard_items + within;
+    }
+    if constexpr (sizeof(G) == 2 && NW == 1) {
+      if (a.stage_bf16) {   // one bf16 gradient per rank: forward the raw item (2 B/elem)
+        uint32_t raw[U][4];
+#pragma unroll
+        for (int j = 0; j < U; ++j)
+          if (ok[j]) ldg_stream_128u(static_cast<const uint16_t *>(a.grad[0]) + item[j] * 8, raw[j]);
+#pragma unroll
+        for (int j = 0; j < U; ++j)
+          if (ok[j]) st_128u(reinterpret_cast<uint16_t *>(a.stage[owner[j]]) + dst[j] * 8, raw[j]);
+        continue;
+      }
+    }
+    float acc[U][8];
+    if constexpr (NW > 0) {
+      float g[NW][U][8];
+#pragma unroll
+      for (int w = 0; w < NW; ++w)
+#pragma unroll
+        for (int j = 0; j < U; ++j)
+          if (ok[j]) load_grad_item<G, true>(a.grad[w], item[j], g[w][j]);
+#pragma unroll
+      for (int j = 0; j < U; ++j)
+#pragma unroll
+        for (int e = 0; e < 8; ++e) {
+          acc[j][e] = g[0][j][e];
+#pragma unroll
+          for (int w = 1; w < NW; ++w) acc[j][e] = __fadd_rn(acc[j][e], g[w][j][e]);
+        }
+    } else {
+      if (ok[0]) load_grad_item<G, true>(a.grad[0], item[0], acc[0]);
+      for (int w0 = 1; w0 < n; w0 += 4) {
+        float g[4][8];
+#pragma unroll
+        for (int q = 0; q < 4; ++q)
+          if (w0 + q < n && ok[0]) load_grad_item<G, true>(a.grad[w0 + q], item[0], g[q]);
+#pragma unroll
+        for (int q = 0; q < 4; ++q)
+          if (w0 + q < n)
+#pragma unroll
+            for (int e = 0; e < 8; ++e) acc[0][e] = __fadd_rn(acc[0][e], g[q][e]);
+      }
+    }
+#pragma unroll
+    for (int j = 0; j < U; ++j)
+      if (ok[j]) st_256(a.stage[owner[j]] + dst[j] * 8, acc[j]);
   }
 }
 
@@ -200,8 +285,9 @@ static int launch_fused_one(const FusedArgs<R> &fa_in, int n_ranks, const TaskSt
                             const Tuning &tune, cudaStream_t s) {
   FusedArgs<R> fa = fa_in;
   const uint64_t items = fa.r[0].shard / 8 * fa.r[0].world;
-  return launch_resident<FusedArgs<R>>(ps_step_fused<G, NW, OPT, R>, fa, n_ranks, ts, 2, items, tune,
-                                       s);
+  // coop = 0: one CTA per SM at most, so the plain launch is possible
+  return launch_resident<FusedArgs<R>>(ps_step_fused<G, NW, OPT, R>, fa, n_ranks, ts,
+                                       tune.coop ? 2 : 1, items, tune, s);
 }
 
 template <typename G, int OPT, int R>

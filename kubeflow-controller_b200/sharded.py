@@ -131,7 +131,10 @@ class SymmBuffer:
         self.nbytes, self.device_index = nbytes, device_index
         dev = torch.device("cuda", device_index)
         group = dist.group.WORLD
-        symm.enable_symm_mem_for_group(group.group_name)
+        import warnings
+        with warnings.catch_warnings():      # newer torch: a deprecated no-op
+            warnings.simplefilter("ignore")
+            symm.enable_symm_mem_for_group(group.group_name)
         self._t = symm.empty(nbytes // 4, dtype=torch.float32, device=dev)
         self._t.zero_()
         self.handle = symm.rendezvous(self._t, group)

@@ -49,6 +49,12 @@ def _worker(rank, world, port, q):
         # 4. round-robin plan agrees across ranks
         rr = pkg.plan_round_robin([78400, 100, 1000, 10], world, 1, 8)
         assert all(x == rr for x in sharded.exchange(rr, world))
+        # 5. the TF-faithful bucket layout of the sharded arena: same on every rank, variable k in
+        #    the shard of rank k mod world
+        lay = sharded.BucketLayout([78400, 100, 1000, 10, 4096, 7], world)
+        views = sharded.exchange((lay.shard, lay.pos), world)
+        assert all(v == views[0] for v in views)
+        assert [p // lay.shard for p in lay.pos] == [k % world for k in range(6)]
         q.put((rank, "ok"))
     except Exception as e:   # surface the failure in the parent
         q.put((rank, repr(e)))

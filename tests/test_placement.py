@@ -304,3 +304,26 @@ def test_local_action_quirks(P):
     assert ev == ("ShouldAddWorker", 1) and composed and rid == "x2456"
     # a succeeded pod wins over everything
     assert P.local_action("mnist", "keep5", 0, 1, "x2456")[0] == ("Nothing", 0)
+
+
+# ---- round-robin buckets as shards of the multi-GPU arena (SURVEY 8 e, TF-faithful mode) ------
+@pytest.mark.parametrize("name", ["resnet50", "bert_large"])
+@pytest.mark.parametrize("world", [1, 2, 4, 8])
+def test_bucket_layout_is_round_robin_padded_to_equal_shards(pkg, name, world):
+    import json
+    import os
+
+    import numpy as np
+    from kubeflow_controller_b200.sharded import BucketLayout
+    shapes = json.load(open(os.path.join(os.path.dirname(__file__), "golden",
+                                         "model_shapes.json")))[name]
+    sizes = [int(np.prod(s)) if s else 1 for _, s in shapes]
+    lay = BucketLayout(sizes, world)
+    task, off, fill = PO.round_robin(sizes, world, 0, 8)
+    assert lay.task == task and lay.offset == off and lay.fill == fill
+    assert lay.shard % 8 == 0 and lay.shard >= max(fill) and lay.shard - max(fill) < 8
+    assert lay.arena == lay.shard * world
+    spans = sorted((lay.pos[k], lay.pos[k] + sizes[k]) for k in range(len(sizes)))
+    assert all(a[1] <= b[0] for a, b in zip(spans, spans[1:])), "variables overlap"
+    for k in range(len(sizes)):
+        assert lay.pos[k] // lay.shard == k % world == (lay.pos[k] + sizes[k] - 1) // lay.shard

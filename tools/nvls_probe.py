@@ -47,12 +47,14 @@ def main():
     loc = torch.randn(2 * shard, device=dev)
     stream = torch.cuda.current_stream()
     peer = buf.peer_ptrs[(rank + 1) % world]
-    for mode, name, kind in MODES:
+    only = os.environ.get("PROBE_MODES")
+    modes = [m for m in MODES if not only or str(m[0]) in only.split(",")]
+    for mode, name, kind in modes:
         if kind == "mc" and not (buf.multicast_ptr and buf2.multicast_ptr):
             if rank == 0:
                 print(json.dumps({"op": name, "skipped": "no multicast mapping on this fabric"}))
             continue
-        for ctas in (148, 296, 592, 1184):
+        for ctas in [int(c) for c in os.environ.get("PROBE_CTAS", "148,296,592,1184").split(",")]:
             def go():
                 base = peer if kind == "uni" else buf.multicast_ptr
                 rc = fn(base, loc.data_ptr(), buf2.multicast_ptr or None, rank * shard, shard, mode,

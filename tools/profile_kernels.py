@@ -51,6 +51,18 @@ def main():
     order += ["ps_wait_pull", "ps_wait_pull"]
     sharded.local_group_step_fused(ranks, grads, n_slices=4)
     order.append("ps_step_fused SGD f32 N=8, 2 ranks in one cooperative launch, 4 slices")
+    sharded.local_group_step_fused(ranks, grads, n_slices=8, overlap=pkg.accel.OVERLAP_SWITCH)
+    order.append("ps_step_switch SGD f32 N=8, 2 ranks in one cooperative launch, 8 slices "
+                 "(peer-load form: no NVSwitch inside one GPU)")
+    torch.cuda.synchronize()
+    del ranks, grads, g32
+    torch.cuda.empty_cache()
+    # config 4's push with raw-bf16 stage slots: one bf16 gradient per rank, 8 ranks on this GPU
+    n4 = 41_892_736 * 8 // 4        # a quarter of BERT-large keeps 8 emulated ranks in memory
+    ranks = sharded.local_group(8, n4, pkg.OPT_ADAM, lambda: pkg.HParams(lr=1e-4))
+    g16 = [[(torch.randn(ranks[0].padded, device=DEV) * 0.01).to(torch.bfloat16)] for _ in ranks]
+    sharded.local_group_step_fused(ranks, g16, n_slices=2)
+    order.append("ps_step_fused Adam bf16 N=1 raw-bf16 stage, 8 ranks in one cooperative launch")
     torch.cuda.synchronize()
     for i, o in enumerate(order):
         print(i, o)
