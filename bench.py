@@ -21,6 +21,7 @@ config. One JSON line on stdout (rank 0).
 from __future__ import annotations
 
 import argparse
+import gc
 import json
 import os
 import subprocess
@@ -457,6 +458,7 @@ def sharded_case(torch, dist, pkg, ShardedPS, rank, world, local, dev, stream, l
     if shard * 4 <= (16 << 20):
         row["bound"] = "latency (cross-GPU signalling dominates; not a bandwidth measurement)"
     del sps, g, grads
+    gc.collect()
     torch.cuda.empty_cache()
     return row
 
@@ -470,6 +472,7 @@ def sharded_configs(torch, dist, pkg, ShardedPS, rank, world, local, dev, stream
                                      *a, **k))
         except Exception as e:   # noqa: BLE001 — one failing case must not lose the line
             rows.append({"workload": a[0], "mode": a[5], "error": f"{type(e).__name__}: {e}"[:300]})
+            gc.collect()
             torch.cuda.empty_cache()
     modes = ["fused", "switch", "nccl"]
     # config 3: ResNet-50-shaped, Momentum, one gradient per rank, PS sharded over the ranks
@@ -676,7 +679,7 @@ def main():
                     help="multi-GPU step form (default: the measured-best per world size)")
     ap.add_argument("--chunks", type=int, default=0,
                     help="pipeline slices of the sharded step (0 = the harness default per world)")
-    ap.add_argument("--host-slices", type=int, default=16,
+    ap.add_argument("--host-slices", type=int, default=32,
                     help="slices of the host-buffer sharded step (e2e leg)")
     ap.add_argument("--rendezvous", default="ipc", choices=["ipc", "symm"])
     ap.add_argument("--overlap", type=int, default=-1, choices=[-1, 0, 1],

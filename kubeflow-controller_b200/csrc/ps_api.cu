@@ -3,6 +3,7 @@
 #include <math.h>
 #include <stdarg.h>
 #include <stdio.h>
+#include <stdlib.h>
 #include <string.h>
 
 #include <algorithm>
@@ -209,6 +210,8 @@ int accel_ctx_create(const int *gpu_ordinals, int n_ps, accel_ctx **out) {
   accel_ctx *c = new (std::nothrow) accel_ctx();
   if (!c) return fail(ACCEL_ERR_NOMEM, "out of host memory");
   c->n_ps = n_ps;
+  const char *tr = getenv("ACCEL_STEP_TRACE");   // development knob, see DESIGN.md
+  c->tuning.trace = tr && tr[0] == '1';
   for (int i = 0; i < n_ps; ++i) {
     c->gpu[i] = gpu_ordinals ? gpu_ordinals[i] : i;
     if (c->gpu[i] < 0) {

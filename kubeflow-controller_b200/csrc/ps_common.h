@@ -26,6 +26,7 @@ struct Tuning {
   int unroll = 0;
   int reducer_pct = 0;  // in-switch step: share of CTAs that reduce+apply+pull (0 = default 25)
   int coop = 1;         // one-kernel step: cooperative launch (0: plain launch for grids <= SMs)
+  int trace = 0;        // development: the in-switch step stamps %globaltimer into flag words 128..255
 };
 
 constexpr int kReducePartials = 4096;  // upper bound on CTAs of the sum-of-squares grid

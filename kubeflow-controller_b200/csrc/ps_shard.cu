@@ -328,11 +328,14 @@ static int do_push(accel_ctx *ctx, const accel_peers *peers, const void *const *
   if (rc) return rc;
   rc = fill_grads(grads, n_workers, grad_dtype, &a);
   if (rc) return rc;
-  a.epoch = ++ts->shard_epoch;  // every push opens a new epoch
-  if (epoch_out) *epoch_out = a.epoch;
+  a.epoch = ts->shard_epoch + 1;  // every push opens a new epoch ...
   if (ctx->tuning.ctas_per_sm) ctas_per_sm = ctx->tuning.ctas_per_sm;   // sweep knob
   const int grid = grid_for(*ts, a.sub_count / 8 * a.world, ctas_per_sm);
-  return grad_dtype == ACCEL_BF16 ? launch_push<bf16_t>(a, grid, s) : launch_push<float>(a, grid, s);
+  rc = grad_dtype == ACCEL_BF16 ? launch_push<bf16_t>(a, grid, s) : launch_push<float>(a, grid, s);
+  if (rc) return rc;
+  ts->shard_epoch = a.epoch;      // ... once its launch has succeeded: a failed launch leaves this
+  if (epoch_out) *epoch_out = a.epoch;   // rank in step with its peers
+  return ACCEL_OK;
 }
 
 static int do_apply_pull(accel_ctx *ctx, const accel_peers *peers, int optimizer, float *slot0,

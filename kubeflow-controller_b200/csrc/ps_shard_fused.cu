@@ -85,7 +85,7 @@ __device__ __forceinline__ void push_slice(const ShardArgs &a, uint64_t sub_firs
   // items in flight per thread: the 4- and 8-gradient forms already have that many loads
   // outstanding; with one or two gradient streams a thread takes several items at once so that
   // neither HBM latency nor the link's is exposed (matters most for small shards)
-  constexpr int U = (NW == 1) ? 4 : (NW == 2) ? 2 : 1;
+  constexpr int U = (NW == 1) ? 2 : 1;   // 4 spills under the 128-register cap of 2 CTAs/SM
   if constexpr (U == 1) {
     push_slice_one<G, NW>(a, sub_first, sub_items, bid, nb);
     return;
@@ -381,6 +381,7 @@ int accel_shard_step_fused(accel_ctx *ctx, const accel_peers *peers, int optimiz
   fa.n_slices = clamp_slices(n_slices, peers->shard_elems);
   fa.roles = overlap == ACCEL_OVERLAP_ROLES;
   fa.n_reducers = reducers_for(ctx->tuning, 0);   // percent; the launcher turns it into CTAs
+  fa.trace = ctx->tuning.trace;
   fa.epoch_base = ts->shard_epoch;
   fa.ctas_per_rank = 0;
   cudaStream_t s = static_cast<cudaStream_t>(stream);
@@ -433,6 +434,7 @@ int accel_shard_step_local_group(accel_ctx *ctx, const accel_peers *const *peers
   fa.n_slices = clamp_slices(n_slices, peers_of_rank[0]->shard_elems);
   fa.roles = overlap == ACCEL_OVERLAP_ROLES;
   fa.n_reducers = reducers_for(ctx->tuning, 0);
+  fa.trace = 0;
   fa.epoch_base = ts0->shard_epoch;
   cudaStream_t s = static_cast<cudaStream_t>(stream);
   const int rc = overlap == ACCEL_OVERLAP_SWITCH

@@ -20,6 +20,7 @@ struct FusedArgs {
   int n_slices;
   int roles;  // ACCEL_OVERLAP_ROLES: even CTAs only push, odd CTAs only apply+pull
   int n_reducers;  // ACCEL_OVERLAP_SWITCH: CTAs per rank that reduce + apply + pull; the rest sum
+  int trace;       // development: stamp %globaltimer into flag words [128, 256)
   uint32_t epoch_base;  // slice k is published as epoch_base + k + 1, the pull as epoch_base + n_slices
 };
 
@@ -88,9 +89,10 @@ __device__ inline void close_step(const ShardArgs &a, uint32_t *flags, int nb, u
 // more CTAs than there is work for (small shards: fewer tickets and fences per step).
 template <typename Args>
 static int size_resident(void (*kern)(const Args), int n_ranks, const TaskState &ts,
-                         int ctas_per_sm_cap, uint64_t work_items, int *per_rank_out) {
+                         int ctas_per_sm_cap, uint64_t work_items, int *per_rank_out,
+                         int threads = kFusedThreads) {
   int per_sm = 0;
-  ACCEL_CUDA(cudaOccupancyMaxActiveBlocksPerMultiprocessor(&per_sm, kern, kFusedThreads, 0));
+  ACCEL_CUDA(cudaOccupancyMaxActiveBlocksPerMultiprocessor(&per_sm, kern, threads, 0));
   if (per_sm < 1) return fail(ACCEL_ERR_CUDA, "one-kernel step does not fit on an SM");
   if (per_sm > ctas_per_sm_cap) per_sm = ctas_per_sm_cap;
   const int resident = per_sm * ts.sm_count;
@@ -108,16 +110,16 @@ static int size_resident(void (*kern)(const Args), int n_ranks, const TaskState 
 // the GPU, and every wait is bounded).
 template <typename Args>
 static int launch_sized(void (*kern)(const Args), Args &fa, int n_ranks, const TaskState &ts,
-                        const Tuning &tune, cudaStream_t s) {
+                        const Tuning &tune, cudaStream_t s, int threads = kFusedThreads) {
   const int grid = fa.ctas_per_rank * n_ranks;
   if (!tune.coop && grid <= ts.sm_count) {
-    kern<<<grid, kFusedThreads, 0, s>>>(fa);
+    kern<<<grid, threads, 0, s>>>(fa);
     ACCEL_CUDA(cudaGetLastError());
     return ACCEL_OK;
   }
   void *params[] = {&fa};
   ACCEL_CUDA(cudaLaunchCooperativeKernel(reinterpret_cast<void *>(kern), dim3(grid),
-                                         dim3(kFusedThreads), params, 0, s));
+                                         dim3(threads), params, 0, s));
   return ACCEL_OK;
 }
 

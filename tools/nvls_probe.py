@@ -27,7 +27,8 @@ MODES = [(2, "local copy (HBM reference)", "none"),
          (6, "peer store bulk-async 4 KiB cp.async.bulk (right neighbour)", "uni"),
          (0, "multimem.st own shard (all-gather pattern)", "mc"),
          (1, "multimem.ld_reduce own shard (reduce-scatter pattern)", "mc"),
-         (7, "ld_reduce own shard + multimem.st of the result (in-switch steady state)", "mc")]
+         (7, "ld_reduce own shard + multimem.st of the result (in-switch steady state)", "mc"),
+         (8, "ld_reduce (even CTAs) and multimem.st (odd CTAs) of the own shard, decoupled", "mc")]
 
 
 def main():

@@ -14,6 +14,9 @@
 //         request instead of 128 stores of 32 B
 // mode 7: mode 1 + mode 0 in one loop (ld_reduce own shard of `mc`, multimem.st it to `mc2`): the
 //         steady state of the in-switch step, both link directions busy at once
+// mode 8: the same two operations DECOUPLED: even CTAs only ld_reduce the own shard of `mc` (into
+//         `local`), odd CTAs only multimem.st the own shard (from `local`) to `mc2` — is the
+//         fabric full-duplex when no thread waits for a reduce before it may store?
 #include <cuda_runtime.h>
 #include <stdint.h>
 
@@ -89,6 +92,21 @@ __global__ void __launch_bounds__(256) probe(float *mc, float *local, float *mc2
       }
     }
     if (lane == 0) asm volatile("cp.async.bulk.wait_group 0;" ::: "memory");
+  } else if constexpr (MODE == 8) {
+    const uint64_t n4 = n_elems / 4;
+    const uint64_t half = gridDim.x / 2;
+    const bool reducer = (blockIdx.x & 1) == 0;
+    for (uint64_t i = static_cast<uint64_t>(blockIdx.x >> 1) * blockDim.x + threadIdx.x; i < n4;
+         i += half * blockDim.x) {
+      float v[4];
+      if (reducer) {
+        mc_ldred128(mc + shard_off + i * 4, v);
+        st128(local + i * 4, v);
+      } else {
+        ld128(local + n4 * 4 + i * 4, v);
+        mc_st128(mc2 + shard_off + i * 4, v);
+      }
+    }
   } else {
     const uint64_t n4 = n_elems / 4;
     for (uint64_t i = static_cast<uint64_t>(blockIdx.x) * blockDim.x + threadIdx.x; i < n4;
@@ -140,6 +158,7 @@ extern "C" int accel_probe_run(float *mc, float *local, float *mc2, uint64_t sha
       break;
     }
     case 7: probe<7><<<ctas, 256, 0, s>>>(mc, local, mc2, shard_off_elems, n_elems); break;
+    case 8: probe<8><<<ctas, 256, 0, s>>>(mc, local, mc2, shard_off_elems, n_elems); break;
     default: return -1;
   }
   return cudaGetLastError() == cudaSuccess ? 0 : -3;

@@ -78,6 +78,61 @@ def main():
         del grads
         torch.cuda.empty_cache()
 
+    if "tune" in what:
+        # second pass over the in-switch step: reducer share x quads in flight x slices
+        padded = -(-ELEMS // (8 * world)) * 8 * world
+        grads = [torch.randn(padded, device=dev) * 0.01 for _ in range(WORKERS)]
+        for slices, pct, unroll in ((8, 6, 4), (8, 8, 4), (8, 10, 4), (6, 6, 4), (12, 6, 4), (8, 4, 4)):
+            try:
+                sps = ShardedPS(rank, world, local, ELEMS, pkg.OPT_SGD, pkg.HParams(lr=0.01),
+                                mode="switch", n_chunks=slices)
+                sps.ctx.set_step_shape(pct, True)
+                ms = timed(lambda: sps.step(grads, stream), 20, 4, stream, dev)
+                sps.check(stream)
+                emit({"case": "headline, in-switch step", "world": world, "slices": slices,
+                      "reducer_pct": pct, "quads_in_flight": unroll, "ms": round(ms, 4)})
+                del sps
+            except Exception as e:   # noqa: BLE001
+                emit({"case": "tune", "slices": slices, "pct": pct, "error": str(e)[:300]})
+            torch.cuda.empty_cache()
+        del grads
+        torch.cuda.empty_cache()
+
+    if "trace" in what:
+        # where the time of one in-switch step goes (ACCEL_STEP_TRACE stamps, microseconds from the
+        # first reducer's start), ranks 0 and world-1
+        os.environ["ACCEL_STEP_TRACE"] = "1"
+        padded = -(-ELEMS // (8 * world)) * 8 * world
+        grads = [torch.randn(padded, device=dev) * 0.01 for _ in range(WORKERS)]
+        for slices, pct, unroll in ((8, 6, 4), (8, 25, 4)):
+            sps = ShardedPS(rank, world, local, ELEMS, pkg.OPT_SGD, pkg.HParams(lr=0.01),
+                            mode="switch", n_chunks=slices)
+            sps.ctx.set_step_shape(pct, True)
+            for _ in range(6):
+                sps.step(grads, stream)
+            sps.check(stream)
+            torch.cuda.synchronize()
+            dist.barrier()
+            t = sps.flags[128:256].view(torch.int64).cpu().tolist()
+            t0 = t[0]
+            row = {"case": "trace of one in-switch step (us from reducer start)", "rank": rank,
+                   "slices": slices, "reducer_pct": pct, "quads_in_flight": unroll,
+                   "summed": [round((x - t0) / 1e3, 1) for x in t[1:1 + slices]],
+                   "reduce_start": [round((x - t0) / 1e3, 1) for x in t[17:17 + slices]],
+                   "reduce_end": [round((x - t0) / 1e3, 1) for x in t[33:33 + slices]],
+                   "closing_ticket": round((t[49] - t0) / 1e3, 1),
+                   "closed": round((t[50] - t0) / 1e3, 1)}
+            rows = [None] * world
+            dist.all_gather_object(rows, row)
+            if rank == 0:
+                for r in (rows[0], rows[world - 1]):
+                    print(json.dumps(r), flush=True)
+            del sps
+            torch.cuda.empty_cache()
+        os.environ.pop("ACCEL_STEP_TRACE", None)
+        del grads
+        torch.cuda.empty_cache()
+
     if "small" in what:
         # small shards: what the launch kind and the grid size cost (one gradient per rank)
         for mib in (1, 16):
