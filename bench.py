@@ -431,11 +431,28 @@ def parity_check(torch, dist, pkg, sps, grads, world, rank, dev, exact):
 
 
 def sharded_case(torch, dist, pkg, ShardedPS, rank, world, local, dev, stream, label, elems, opt,
-                 bf16, hpkw, mode, slices, pull="f32", steps=20, warmup=4):
+                 bf16, hpkw, mode, slices, pull="f32", steps=20, warmup=4, in_place=False):
+    # every rank must take the same decision (a rank that fails alone would leave the others
+    # waiting in the rendezvous): agree on the smallest free memory first
+    padded_est = -(-elems // (8 * world)) * 8 * world
+    need = padded_est * (4 + 4 + (2 if bf16 else 4) + (4 if bf16 else 0) + (2 if pull == "bf16" else 0)) \
+        + padded_est // world * 4 * opt
+    gc.collect()
+    torch.cuda.empty_cache()
+    free = torch.tensor([torch.cuda.mem_get_info()[0]], device=dev, dtype=torch.int64)
+    dist.all_reduce(free, op=dist.ReduceOp.MIN)
+    if need * 1.08 > free.item():
+        return {"workload": label, "ps_shards": world, "mode": mode,
+                "skipped": f"needs {need / 2**30:.1f} GiB per GPU, {free.item() / 2**30:.1f} GiB free"}
     sps = ShardedPS(rank, world, local, elems, opt, pkg.HParams(**hpkw), mode=mode,
                     n_chunks=slices or None, pull_dtype=pull)
     g = torch.randn(sps.padded, device=dev).mul_(0.01)
-    grads = [g.to(torch.bfloat16) if bf16 else g]
+    if in_place:     # zero-copy in-switch form: the worker's gradient lives in the stage buffer
+        view = sps.stage_grad(torch.bfloat16 if bf16 else torch.float32)
+        view.copy_(g)
+        grads = [view]
+    else:
+        grads = [g.to(torch.bfloat16) if bf16 else g]
     ms = timed_steps(torch, dist, lambda: sps.step(grads, stream), steps, warmup, stream, dev)
     if mode != "nccl":
         sps.check(stream)
@@ -447,7 +464,8 @@ def sharded_case(torch, dist, pkg, ShardedPS, rank, world, local, dev, stream, l
         link = (world - 1) * shard * (4 + pb)
     else:
         link = (world - 1) * shard * (gb + pb)
-    row = {"workload": label, "ps_shards": world, "mode": mode, "slices": sps.n_chunks,
+    row = {"workload": label, "ps_shards": world, "mode": mode + (" in place" if in_place else ""),
+           "slices": sps.n_chunks,
            "pull": pull, "opt": ["sgd", "momentum", "adam"][opt], "grad": "bf16" if bf16 else "f32",
            "elems": elems, "shard_mib": round(shard * 4 / 2**20, 2), "ms": round(ms, 4),
            "steps_per_s": round(1e3 / ms, 1), "nvlink_bytes_per_gpu_per_dir": link,
@@ -479,6 +497,8 @@ def sharded_configs(torch, dist, pkg, ShardedPS, rank, world, local, dev, stream
     for mode in modes:
         add(f"cfg3 ResNet-50-shaped (25.6M fp32) Momentum, {world} PS shards", RESNET50_ELEMS,
             pkg.OPT_MOMENTUM, False, dict(lr=0.1, momentum=0.9), mode, 1 if mode != "switch" else 2)
+    add(f"cfg3 ResNet-50-shaped (25.6M fp32) Momentum, {world} PS shards", RESNET50_ELEMS,
+        pkg.OPT_MOMENTUM, False, dict(lr=0.1, momentum=0.9), "switch", 2, in_place=True)
     # the same model placed the reference's way (variable k -> PS task k mod P, buckets padded to
     # equal length): same kernels, a larger and unbalanced arena
     try:
@@ -497,6 +517,9 @@ def sharded_configs(torch, dist, pkg, ShardedPS, rank, world, local, dev, stream
         add(f"cfg4 BERT-large-shaped (335M) bf16 grads -> fp32 Adam, {world} PS shards",
             BERT_LARGE_ELEMS, pkg.OPT_ADAM, True, dict(lr=1e-4), mode,
             4 if mode == "switch" else 2, pull=pull, steps=10, warmup=3)
+    add(f"cfg4 BERT-large-shaped (335M) bf16 grads -> fp32 Adam, {world} PS shards",
+        BERT_LARGE_ELEMS, pkg.OPT_ADAM, True, dict(lr=1e-4), "switch", 4, steps=10, warmup=3,
+        in_place=True)
     # config 5: fp32 variable shards of 1 MiB - 4 GiB per GPU, one gradient per rank
     sizes = (1, 4, 16, 64, 256, 1024) + ((4096,) if big else ())
     for mib in sizes:
@@ -508,6 +531,9 @@ def sharded_configs(torch, dist, pkg, ShardedPS, rank, world, local, dev, stream
                 add(f"cfg5 {mib} MiB fp32 shard per GPU, {world} PS shards", (mib << 18) * world, opt,
                     False, hpkw, mode, 1 if mode == "fused" else (1 if mib <= 16 else 4),
                     steps=n if mib < 4096 else 4, warmup=3)
+            if mib < 4096 and opt == pkg.OPT_SGD:
+                add(f"cfg5 {mib} MiB fp32 shard per GPU, {world} PS shards", (mib << 18) * world, opt,
+                    False, hpkw, "switch", 1 if mib <= 16 else 4, steps=n, warmup=3, in_place=True)
     return rows
 
 

@@ -510,7 +510,11 @@ int accel_shard_step(accel_ctx *ctx, const accel_peers *peers, int optimizer, fl
  *         stage_multicast and var_multicast. When both are NULL the same
  *         protocol runs with `world` peer loads summed in rank order and
  *         `world` peer stores instead (bit-exact; the form a single GPU can run
- *         under accel_shard_step_local_group). */
+ *         under accel_shard_step_local_group). Zero-copy: with n_workers = 1 the
+ *         caller may pass its own stage buffer as the gradient (grads[0] ==
+ *         stage[rank], arena layout, fp32 — or bf16 with stage_dtype ACCEL_BF16):
+ *         the worker then writes its gradient where the switch reads it and the
+ *         step copies nothing. The other forms reject that aliasing. */
 typedef enum accel_overlap {
   ACCEL_OVERLAP_INLINE = 0,
   ACCEL_OVERLAP_ROLES = 1,

@@ -262,6 +262,20 @@ int fill_grads(const void *const *grads, int n_workers, int grad_dtype, ShardArg
     a->grad[w] = grads[w];
   }
   a->n_workers = n_workers;
+  // zero-copy form of the in-switch step: the worker wrote its gradient straight into this rank's
+  // stage buffer (arena layout), so there is nothing to sum or copy before the switch reads it
+  a->in_place = n_workers == 1 && grads[0] == static_cast<const void *>(a->stage[a->rank]) &&
+                (grad_dtype == ACCEL_F32 || a->stage_bf16);
+  // any other overlap of a gradient with the stage buffer is a race (peers write into it)
+  const char *lo = reinterpret_cast<const char *>(a->stage[a->rank]);
+  const char *hi = lo + static_cast<size_t>(a->shard) * a->world * sizeof(float);
+  for (int w = 0; w < n_workers; ++w) {
+    const char *g = static_cast<const char *>(grads[w]);
+    if (g >= lo && g < hi && !a->in_place)
+      return fail(ACCEL_ERR_INVALID,
+                  "grads[%d] lies inside this rank's stage buffer; only the in-switch step accepts "
+                  "that, with n_workers = 1 and grads[0] == stage[rank]", w);
+  }
   if (a->stage_bf16 && !(grad_dtype == ACCEL_BF16 && n_workers == 1))
     return fail(ACCEL_ERR_INVALID,
                 "stage_dtype ACCEL_BF16 carries ONE raw bf16 gradient per rank; got n_workers %d, "
@@ -328,6 +342,10 @@ static int do_push(accel_ctx *ctx, const accel_peers *peers, const void *const *
   if (rc) return rc;
   rc = fill_grads(grads, n_workers, grad_dtype, &a);
   if (rc) return rc;
+  if (a.in_place)
+    return fail(ACCEL_ERR_INVALID,
+                "the gradient is this rank's stage buffer: peers overwrite it during a unicast push; "
+                "only ACCEL_OVERLAP_SWITCH runs in place");
   a.epoch = ts->shard_epoch + 1;  // every push opens a new epoch ...
   if (ctx->tuning.ctas_per_sm) ctas_per_sm = ctx->tuning.ctas_per_sm;   // sweep knob
   const int grid = grid_for(*ts, a.sub_count / 8 * a.world, ctas_per_sm);

@@ -29,6 +29,7 @@ struct ShardArgs {
   float *var_mc;   // multicast mapping of all ranks' var replicas, or nullptr
   float *stage_mc; // multicast mapping of all ranks' stage buffers (in-switch step), or nullptr
   int stage_bf16;  // stage slots hold raw bf16 (one bf16 gradient per rank); else fp32 partials
+  int in_place;    // in-switch step: the single local gradient already IS this rank's stage buffer
   uint16_t *var_bf16[ACCEL_MAX_PS];  // bf16 replicas (pull target) or all nullptr
   uint64_t shard;  // elements per shard, multiple of 8
   uint64_t sub_begin, sub_count;  // the slice of EVERY shard this launch covers (multiples of 8)

@@ -389,6 +389,10 @@ int accel_shard_step_fused(accel_ctx *ctx, const accel_peers *peers, int optimiz
     rc = check_switch(peers, fa.r[0]);
     if (rc) return rc;
     rc = launch_switch(fa, optimizer, grad_dtype, *ts, ctx->tuning, s);
+  } else if (fa.r[0].in_place) {
+    return fail(ACCEL_ERR_INVALID,
+                "the gradient is this rank's stage buffer: peers overwrite it during a unicast push; "
+                "only ACCEL_OVERLAP_SWITCH runs in place");
   } else {
     rc = launch_fused<1>(fa, 1, optimizer, grad_dtype, *ts, ctx->tuning, s);
   }
@@ -427,6 +431,8 @@ int accel_shard_step_local_group(accel_ctx *ctx, const accel_peers *const *peers
                    slot1 ? slot1[r] : nullptr, grads[r], n_workers, grad_dtype, n_contrib, hp,
                    grad_sumsq_dev, &fa.r[r]);
     if (rc) return rc;
+    if (overlap != ACCEL_OVERLAP_SWITCH && fa.r[r].in_place)
+      return fail(ACCEL_ERR_INVALID, "only ACCEL_OVERLAP_SWITCH runs in place (rank %d)", r);
     if (overlap == ACCEL_OVERLAP_SWITCH && (fa.r[r].stage_mc || fa.r[r].var_mc))
       return fail(ACCEL_ERR_INVALID,
                   "a local group has no NVSwitch between its ranks: multicast pointers must be NULL");

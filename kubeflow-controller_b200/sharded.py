@@ -269,6 +269,14 @@ class ShardedPS:
         self.solo = accel.Peers(0, 1, self.padded, self._solo_stage, self._solo_var,
                                 self._solo_flags, None, None, None, accel.F32, 0)
 
+    def stage_grad(self, dtype=torch.float32) -> torch.Tensor:
+        """The view of this rank's stage buffer a worker can write its ONE gradient into (arena
+        layout), for the zero-copy form of the in-switch step: pass it back as the only gradient of
+        step() and nothing is copied before the switch reads it. bf16 needs bf16_stage."""
+        if dtype == torch.bfloat16:
+            return self.stage.view(torch.bfloat16)[:self.padded]
+        return self.stage[:self.padded]
+
     @property
     def var_shard(self) -> torch.Tensor:
         return self.var[self.rank * self.shard:(self.rank + 1) * self.shard]

@@ -373,3 +373,47 @@ def test_rank_runs_on_the_device_it_was_given(pkg):
     x = sharded.ShardedPS(1, 2, 0, 4096, pkg.OPT_SGD, pkg.HParams(lr=1.0),
                           peer_ptrs=[(0, 0, 0, 0)] * 2)
     assert x.ctx.gpu_of(1) == 0
+
+
+@pytest.mark.parametrize("world,slices", [(2, 1), (4, 3), (8, 8)])
+@pytest.mark.parametrize("bf16", [False, True])
+def test_in_switch_step_in_place(pkg, world, slices, bf16):
+    """Zero-copy form of the in-switch protocol: every rank's single gradient is written straight
+    into its own stage buffer and passed as grads[0]; nothing is copied, the reduce reads it
+    there. Same bits as the copying form (peer-load emulation on one GPU)."""
+    from kubeflow_controller_b200 import sharded
+    opt = O.ADAM
+    ranks = sharded.local_group(world, 60_001, opt, lambda: pkg.HParams(lr=0.01))
+    padded, shard = ranks[0].padded, ranks[0].shard
+    rng = np.random.default_rng(world + slices)
+    var = rng.standard_normal(padded).astype(F)
+    s0, s1 = np.zeros(padded, F), np.zeros(padded, F)
+    for x in ranks:
+        x.var.copy_(_dev(var))
+    ohp = O.HParams(lr=0.01)
+    for step in range(2):
+        gpr = [[(0.01 * rng.standard_normal(padded)).astype(F)] for _ in range(world)]
+        if bf16:
+            gpr = [[O.f32_to_bf16_bits(g[0])] for g in gpr]
+        dg = []
+        for x, g in zip(ranks, gpr):
+            view = x.stage_grad(torch.bfloat16 if bf16 else torch.float32)
+            view.copy_(_dev(g[0]))
+            dg.append([view])
+        sharded.local_group_step_fused(ranks, dg, n_slices=slices, overlap=2)
+        O.numpy_apply(opt, var, s0, s1, _oracle_hier(gpr, False), ohp)
+        ohp.advance()
+    for x in ranks:
+        assert np.array_equal(x.var.cpu().numpy(), var), f"rank {x.rank} replica differs"
+
+
+def test_gradient_inside_stage_is_rejected_by_unicast_forms(pkg):
+    from kubeflow_controller_b200 import sharded
+    ranks = sharded.local_group(2, 4096, pkg.OPT_SGD, lambda: pkg.HParams(lr=1.0))
+    dg = [[x.stage_grad()] for x in ranks]
+    with pytest.raises(pkg.AccelError, match="stage buffer"):
+        ranks[0].push(dg[0])
+    with pytest.raises(pkg.AccelError, match="in place"):
+        sharded.local_group_step_fused(ranks, dg, n_slices=1, overlap=0)
+    with pytest.raises(pkg.AccelError, match="stage buffer"):
+        ranks[0].push([ranks[0].stage[ranks[0].shard:]])     # anywhere inside it, not just the base

@@ -31,13 +31,18 @@ def main():
     ok = True
     variants = [("fused", "ipc", 1), ("fused", "ipc", 16), ("fused-roles", "ipc", 8),
                 ("fused", "symm", 8), ("streams", "ipc", 4), ("nccl", "ipc", 1),
-                ("switch", "symm", 1), ("switch", "symm", 5), ("host", "ipc", 3)]
+                ("switch", "symm", 1), ("switch", "symm", 5), ("switch-inplace", "symm", 4),
+                ("host", "ipc", 3)]
     if os.environ.get("VERIFY_ONLY"):
         variants = [v for v in variants if v[0] in os.environ["VERIFY_ONLY"].split(",")]
     for mode, rdv, chunks in variants:
         for opt, bf16, workers in ((pkg.OPT_SGD, False, 3), (pkg.OPT_ADAM, True, 3),
-                                   (pkg.OPT_MOMENTUM, False, 8), (pkg.OPT_ADAM, True, 1)):
+                                   (pkg.OPT_MOMENTUM, False, 8), (pkg.OPT_ADAM, True, 1),
+                                   (pkg.OPT_SGD, False, 1)):
             host = mode == "host"
+            inplace = mode == "switch-inplace"
+            if inplace and workers != 1:
+                continue                      # the zero-copy form takes exactly one gradient
             sps = ShardedPS(rank, world, local, elems, opt, pkg.HParams(lr=0.01, momentum=0.9),
                             mode="fused" if host else mode.split("-")[0], rendezvous=rdv,
                             n_chunks=chunks, multicast=False,
@@ -58,6 +63,12 @@ def main():
                     mine = [torch.from_numpy(g.view(np.int16)).view(torch.bfloat16).pin_memory()
                             if bf16 else torch.from_numpy(g).pin_memory() for g in allg[rank]]
                     sps.step_host(mine, None, n_slices=chunks)
+                elif inplace:     # the worker writes its gradient straight into the stage buffer
+                    view = sps.stage_grad(torch.bfloat16 if bf16 else torch.float32)
+                    g0 = allg[rank][0]
+                    view.copy_(torch.from_numpy(g0.view(np.int16)).to(dev).view(torch.bfloat16)
+                               if bf16 else torch.from_numpy(g0).to(dev))
+                    sps.step([view])
                 else:
                     mine = [torch.from_numpy(g.view(np.int16)).to(dev).view(torch.bfloat16) if bf16
                             else torch.from_numpy(g).to(dev) for g in allg[rank]]
@@ -70,10 +81,10 @@ def main():
             torch.cuda.synchronize()
             dist.barrier()
             got = sps.var.cpu().numpy()
-            if mode == "switch" and bf16 and workers == 1:
+            if mode.startswith("switch") and bf16 and workers == 1:
                 good = np.allclose(got, var, rtol=1e-2, atol=1e-4)     # bf16-rounded sums
                 tol = "rel 1e-2"
-            elif mode in ("nccl", "switch"):
+            elif mode == "nccl" or mode.startswith("switch"):
                 good = np.allclose(got, var, rtol=1e-5, atol=1e-6)
                 tol = "rel 1e-5"
             else:
