@@ -439,6 +439,7 @@ def sharded_case(torch, dist, pkg, ShardedPS, rank, world, local, dev, stream, l
         + padded_est // world * 4 * opt
     gc.collect()
     torch.cuda.empty_cache()
+    dist.barrier()      # every rank has dropped (and unmapped) the previous case's buffers
     free = torch.tensor([torch.cuda.mem_get_info()[0]], device=dev, dtype=torch.int64)
     dist.all_reduce(free, op=dist.ReduceOp.MIN)
     if need * 1.08 > free.item():
@@ -475,6 +476,7 @@ def sharded_case(torch, dist, pkg, ShardedPS, rank, world, local, dev, stream, l
            "launches": (steps + warmup) * sps.launches_per_step}
     if shard * 4 <= (16 << 20):
         row["bound"] = "latency (cross-GPU signalling dominates; not a bandwidth measurement)"
+    sps.close()
     del sps, g, grads
     gc.collect()
     torch.cuda.empty_cache()
@@ -632,7 +634,9 @@ def run_sharded(args):
         del h_grads, h_out
     n_chunks, overlap, mc = sps.n_chunks, sps.overlap, bool(sps.multicast_ptr)
     launches_per_step, padded = sps.launches_per_step, sps.padded
+    sps.close()
     del sps, grads
+    gc.collect()
     torch.cuda.empty_cache()
     configs = [] if args.no_configs else sharded_configs(
         torch, dist, pkg, ShardedPS, rank, world, local, dev, stream, big=not args.no_big)

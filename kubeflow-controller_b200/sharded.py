@@ -231,6 +231,7 @@ class ShardedPS:
         n_slices = -(-(self.shard // 8) // (-(-(self.shard // 8) // self.n_chunks)))
         self.launches_per_step = {"fused": 1, "switch": 1, "streams": 2 * n_slices + 1,
                                   "nccl": 2}[mode]
+        self._opened = []     # peers' allocations mapped into this process (accel_ipc_open)
         if peer_ptrs is None:
             mine = (self.buf_var.export(), self.buf_stage.export(), self.buf_flags.export(),
                     self.buf_var16.export() if self.buf_var16 else None)
@@ -242,9 +243,28 @@ class ShardedPS:
                         peer_ptrs.append((self.buf_var.ptr, self.buf_stage.ptr, self.buf_flags.ptr,
                                           self.buf_var16.ptr if self.buf_var16 else 0))
                     else:
-                        peer_ptrs.append((open_peer(hv), open_peer(hs), open_peer(hf),
-                                          open_peer(h16) if h16 else 0))
+                        mapped = (open_peer(hv), open_peer(hs), open_peer(hf),
+                                  open_peer(h16) if h16 else 0)
+                        self._opened += [m for m in mapped if m]
+                        peer_ptrs.append(mapped)
         self.set_peers(peer_ptrs)
+
+    def close(self):
+        """Unmap the peers' buffers. An exported allocation is only returned to the device once
+        every process that mapped it has closed its handle, so a rank that drops its ShardedPS
+        without this keeps its peers' memory alive."""
+        opened, self._opened = getattr(self, "_opened", []), []
+        if opened:
+            with torch.cuda.device(self.device_index):
+                torch.cuda.synchronize()
+                for ptr in opened:
+                    self.lib.accel_ipc_close(ptr)
+
+    def __del__(self):
+        try:
+            self.close()
+        except Exception:
+            pass
 
     def set_peers(self, peer_ptrs):
         """peer_ptrs[r] = (var, stage, flags) device addresses of rank r as seen from here."""
