@@ -212,6 +212,8 @@ int accel_ctx_create(const int *gpu_ordinals, int n_ps, accel_ctx **out) {
   c->n_ps = n_ps;
   const char *tr = getenv("ACCEL_STEP_TRACE");   // development knob, see DESIGN.md
   c->tuning.trace = tr && tr[0] == '1';
+  const char *l2 = getenv("ACCEL_STEP_L2HINT");
+  c->tuning.l2hint = l2 && l2[0] == '1';
   for (int i = 0; i < n_ps; ++i) {
     c->gpu[i] = gpu_ordinals ? gpu_ordinals[i] : i;
     if (c->gpu[i] < 0) {

@@ -27,6 +27,7 @@ struct Tuning {
   int reducer_pct = 0;  // in-switch step: share of CTAs that reduce+apply+pull (0 = default 25)
   int coop = 1;         // one-kernel step: cooperative launch (0: plain launch for grids <= SMs)
   int trace = 0;        // development: the in-switch step stamps %globaltimer into flag words 128..255
+  int l2hint = 0;       // development: L2 policies on the summers' loads and stores (ACCEL_STEP_L2HINT)
 };
 
 constexpr int kReducePartials = 4096;  // upper bound on CTAs of the sum-of-squares grid

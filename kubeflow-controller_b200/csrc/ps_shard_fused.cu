@@ -382,6 +382,7 @@ int accel_shard_step_fused(accel_ctx *ctx, const accel_peers *peers, int optimiz
   fa.roles = overlap == ACCEL_OVERLAP_ROLES;
   fa.n_reducers = reducers_for(ctx->tuning, 0);   // percent; the launcher turns it into CTAs
   fa.trace = ctx->tuning.trace;
+  fa.l2hint = ctx->tuning.l2hint;
   fa.epoch_base = ts->shard_epoch;
   fa.ctas_per_rank = 0;
   cudaStream_t s = static_cast<cudaStream_t>(stream);
@@ -441,6 +442,7 @@ int accel_shard_step_local_group(accel_ctx *ctx, const accel_peers *const *peers
   fa.roles = overlap == ACCEL_OVERLAP_ROLES;
   fa.n_reducers = reducers_for(ctx->tuning, 0);
   fa.trace = 0;
+  fa.l2hint = 0;
   fa.epoch_base = ts0->shard_epoch;
   cudaStream_t s = static_cast<cudaStream_t>(stream);
   const int rc = overlap == ACCEL_OVERLAP_SWITCH

@@ -21,6 +21,7 @@ struct FusedArgs {
   int roles;  // ACCEL_OVERLAP_ROLES: even CTAs only push, odd CTAs only apply+pull
   int n_reducers;  // ACCEL_OVERLAP_SWITCH: CTAs per rank that reduce + apply + pull; the rest sum
   int trace;       // development: stamp %globaltimer into flag words [128, 256)
+  int l2hint;      // development: L2 evict-first gradient loads / evict-last stage stores (summers)
   uint32_t epoch_base;  // slice k is published as epoch_base + k + 1, the pull as epoch_base + n_slices
 };
 

@@ -98,6 +98,31 @@ def main():
         del grads
         torch.cuda.empty_cache()
 
+    if "l2" in what:
+        # ACCEL_STEP_L2HINT: evict-first gradient loads and evict-last stage stores in the summers,
+        # so that the slice the switch reads next is still in L2; off / on, several slice counts
+        padded = -(-ELEMS // (8 * world)) * 8 * world
+        grads = [torch.randn(padded, device=dev) * 0.01 for _ in range(WORKERS)]
+        for hint in ("0", "1"):
+            os.environ["ACCEL_STEP_L2HINT"] = hint
+            for slices, pct in ((8, 6), (8, 12), (16, 12), (32, 12), (16, 25)):
+                try:
+                    sps = ShardedPS(rank, world, local, ELEMS, pkg.OPT_SGD, pkg.HParams(lr=0.01),
+                                    mode="switch", n_chunks=slices)
+                    sps.ctx.set_step_shape(pct, True)
+                    ms = timed(lambda: sps.step(grads, stream), 20, 4, stream, dev)
+                    sps.check(stream)
+                    emit({"case": "headline, in-switch step, L2 policies", "world": world,
+                          "l2hint": int(hint), "slices": slices, "reducer_pct": pct,
+                          "ms": round(ms, 4)})
+                    del sps
+                except Exception as e:   # noqa: BLE001
+                    emit({"case": "l2", "l2hint": hint, "slices": slices, "error": str(e)[:300]})
+                torch.cuda.empty_cache()
+        os.environ.pop("ACCEL_STEP_L2HINT", None)
+        del grads
+        torch.cuda.empty_cache()
+
     if "trace" in what:
         # where the time of one in-switch step goes (ACCEL_STEP_TRACE stamps, microseconds from the
         # first reducer's start), ranks 0 and world-1
