@@ -47,3 +47,18 @@ def test_gpu_arm_refuses_to_run_without_a_gpu():
     p = _run("--steps", "1", "--warmup", "1", "--no-e2e", "--no-cpu")
     assert p.returncode != 0
     assert not [ln for ln in p.stdout.splitlines() if ln.startswith("{")]
+
+
+def test_reference_arm_runs_the_same_config_at_n_gpus():
+    """At N > 1 the reference arm times the CPU path on the SAME N-PS-task workload the GPU arm
+    runs (round 1's arm kept the single-PS job, so the driver's ratio compared unlike things)."""
+    p = _run("--impl", "reference", "--gpus", "2", "--steps", "1", "--warmup", "1",
+             env={"RANK": "0", "WORLD_SIZE": "2", "LOCAL_RANK": "0"})
+    assert p.returncode == 0, p.stderr[-2000:]
+    d = json.loads([ln for ln in p.stdout.splitlines() if ln.startswith("{")][0])
+    sys.path.insert(0, ROOT)
+    import bench
+    assert d["config"] == bench.workload_config(2)
+    assert d["config"]["ps_shards"] == 2 and d["n_gpus"] == 2
+    assert "2 PS tasks back to back" in d["cpu_baseline"]["sample"]
+    assert d["cpu_baseline"]["host_mem_gbs"] > 0
