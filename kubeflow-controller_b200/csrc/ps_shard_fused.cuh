@@ -4,6 +4,7 @@
 #pragma once
 
 #include <cooperative_groups.h>
+#include <stdlib.h>
 
 #include "ps_shard.cuh"
 
@@ -98,7 +99,14 @@ static int size_resident(void (*kern)(const Args), int n_ranks, const TaskState 
   if (per_sm > ctas_per_sm_cap) per_sm = ctas_per_sm_cap;
   const int resident = per_sm * ts.sm_count;
   int per_rank = resident / n_ranks;
-  const uint64_t want = (work_items + 2 * kFusedThreads - 1) / (2 * kFusedThreads);
+  // items per thread below which the grid shrinks (development knob ACCEL_STEP_ITEMS, default 2)
+  static const int items_per_thread = [] {
+    const char *e = getenv("ACCEL_STEP_ITEMS");
+    const int v = e ? atoi(e) : 0;
+    return v >= 1 && v <= 64 ? v : 2;
+  }();
+  const uint64_t per_cta = static_cast<uint64_t>(items_per_thread) * kFusedThreads;
+  const uint64_t want = (work_items + per_cta - 1) / per_cta;
   if (static_cast<uint64_t>(per_rank) > want) per_rank = static_cast<int>(want < 2 ? 2 : want);
   if (per_rank < 1 || per_rank * n_ranks > resident)
     return fail(ACCEL_ERR_INVALID, "%d ranks do not fit in %d resident CTAs", n_ranks, resident);

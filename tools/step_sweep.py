@@ -158,6 +158,26 @@ def main():
         del grads
         torch.cuda.empty_cache()
 
+    if "grid" in what:
+        # small shards: how many items per thread before the grid shrinks (ACCEL_STEP_ITEMS is read
+        # once per process, so this section takes the value from the environment of the launch)
+        ipt = os.environ.get("ACCEL_STEP_ITEMS", "2")
+        for mib in (1, 4):
+            elems = (mib << 18) * world
+            g = [torch.randn(elems, device=dev) * 0.01]
+            for mode, coop in (("fused", True), ("fused", False)):
+                sps = ShardedPS(rank, world, local, elems, pkg.OPT_SGD, pkg.HParams(lr=0.01),
+                                mode=mode, n_chunks=1, overlap=0)
+                sps.ctx.set_step_shape(0, coop)
+                ms = timed(lambda: sps.step(g, stream), 100, 10, stream, dev)
+                sps.check(stream)
+                emit({"case": f"grid sizing, {mib} MiB shard, SGD, 1 gradient per rank",
+                      "world": world, "items_per_thread": int(ipt), "coop": coop,
+                      "us": round(ms * 1e3, 2)})
+                del sps
+                torch.cuda.empty_cache()
+            del g
+
     if "small" in what:
         # small shards: what the launch kind and the grid size cost (one gradient per rank)
         for mib in (1, 16):
