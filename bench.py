@@ -716,7 +716,7 @@ def main():
                     help="one-kernel step: 0 = every CTA pushes then applies, 1 = split roles, "
                          "-1 = the harness default per world")
     ap.add_argument("--reducers", type=int, default=0,
-                    help="switch mode: percent of CTAs that reduce+apply+pull (0 = default 25)")
+                    help="switch mode: percent of CTAs that reduce+apply+pull (0 = default: 25 with one local gradient, 8 with several)")
     ap.add_argument("--no-coop", action="store_true",
                     help="one-kernel step: plain launch when the grid is <= one CTA per SM")
     ap.add_argument("--pull", default="f32", choices=["f32", "bf16"],

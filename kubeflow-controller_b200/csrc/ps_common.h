@@ -24,7 +24,7 @@ struct Tuning {
   int threads = 0;
   int ctas_per_sm = 0;
   int unroll = 0;
-  int reducer_pct = 0;  // in-switch step: share of CTAs that reduce+apply+pull (0 = default 25)
+  int reducer_pct = 0;  // in-switch step: share of CTAs that reduce+apply+pull (0 = default)
   int coop = 1;         // one-kernel step: cooperative launch (0: plain launch for grids <= SMs)
   int trace = 0;        // development: the in-switch step stamps %globaltimer into flag words 128..255
   int l2hint = 0;       // development: L2 policies on the summers' loads and stores (ACCEL_STEP_L2HINT)

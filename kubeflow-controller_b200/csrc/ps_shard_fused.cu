@@ -347,20 +347,24 @@ static bool overlap_ok(int overlap) {
 }
 
 // SWITCH on real peers runs through the NVSwitch: both multicast mappings or neither.
-static int check_switch(const accel_peers *peers, const ShardArgs &a) {
+static int check_switch(const ShardArgs &a) {
   if ((a.stage_mc == nullptr) != (a.var_mc == nullptr))
     return fail(ACCEL_ERR_INVALID,
                 "ACCEL_OVERLAP_SWITCH needs stage_multicast AND var_multicast (or neither: the "
                 "peer-load form)");
   if (a.var_bf16[0] != nullptr && a.var_mc != nullptr)
     return fail(ACCEL_ERR_INVALID, "var_bf16 and the multicast pull are mutually exclusive");
-  (void)peers;
   return ACCEL_OK;
 }
 
-static int reducers_for(const Tuning &t, int per_rank_hint) {
-  (void)per_rank_hint;
-  return t.reducer_pct > 0 ? t.reducer_pct : 25;
+// Share of the CTAs that reduce + apply + pull in the in-switch step, in percent. With one local
+// gradient the step is a pure collective and the reducers do all the work that matters: 25 %
+// (the link probe is flat from 74 CTAs up and slower at 37). With several local gradients the
+// HBM-bound summers need the CTAs: 8 % (6-12 % within noise of each other at 8 GPUs, 25 % slower,
+// 3 % starves the links; profiles/r02_sharded_step.md).
+static int reducer_percent(const Tuning &t, int n_workers) {
+  if (t.reducer_pct > 0) return t.reducer_pct;
+  return n_workers == 1 ? 25 : 8;
 }
 
 extern "C" {
@@ -380,14 +384,14 @@ int accel_shard_step_fused(accel_ctx *ctx, const accel_peers *peers, int optimiz
   if (rc) return rc;
   fa.n_slices = clamp_slices(n_slices, peers->shard_elems);
   fa.roles = overlap == ACCEL_OVERLAP_ROLES;
-  fa.n_reducers = reducers_for(ctx->tuning, 0);   // percent; the launcher turns it into CTAs
+  fa.n_reducers = reducer_percent(ctx->tuning, n_workers);   // percent; the launcher turns it into CTAs
   fa.trace = ctx->tuning.trace;
   fa.l2hint = ctx->tuning.l2hint;
   fa.epoch_base = ts->shard_epoch;
   fa.ctas_per_rank = 0;
   cudaStream_t s = static_cast<cudaStream_t>(stream);
   if (overlap == ACCEL_OVERLAP_SWITCH) {
-    rc = check_switch(peers, fa.r[0]);
+    rc = check_switch(fa.r[0]);
     if (rc) return rc;
     rc = launch_switch(fa, optimizer, grad_dtype, *ts, ctx->tuning, s);
   } else if (fa.r[0].in_place) {
@@ -440,7 +444,7 @@ int accel_shard_step_local_group(accel_ctx *ctx, const accel_peers *const *peers
   }
   fa.n_slices = clamp_slices(n_slices, peers_of_rank[0]->shard_elems);
   fa.roles = overlap == ACCEL_OVERLAP_ROLES;
-  fa.n_reducers = reducers_for(ctx->tuning, 0);
+  fa.n_reducers = reducer_percent(ctx->tuning, n_workers);
   fa.trace = 0;
   fa.l2hint = 0;
   fa.epoch_base = ts0->shard_epoch;

@@ -1,11 +1,14 @@
 package accel
 
 /*
+#include <stdlib.h>
 #include "accel_ps.h"
 */
 import "C"
 
 import (
+	"unsafe"
+
 	api "github.com/caicloud/kubeflow-clientset/apis/kubeflow/v1alpha1"
 )
 
@@ -75,4 +78,26 @@ func PlanRoundRobin(varElems []uint64, nPS, firstTask int, alignElems uint64) (t
 		bucket[i] = uint64(cb[i])
 	}
 	return
+}
+
+// LocalAction restates LocalJob.Action (pkg/tensorflow/local.go:50-74) with NewLocalJob's pod
+// selection (:34-48) and compose()/labels() (:78-90). suffix is the 5-character RuntimeID that
+// compose() would draw. It returns the action type (accel_action order), the number of replicas
+// to add, whether compose() ran, and the text block "runtime_id\t<id>\n" + "key=value\n" labels.
+func LocalAction(jobName, runtimeID string, firstSpecType, activePods, succeeded int,
+	suffix string) (action, number int, composed bool, text string, err error) {
+	cj, cr, cs := C.CString(jobName), C.CString(runtimeID), C.CString(suffix)
+	defer C.free(unsafe.Pointer(cj))
+	defer C.free(unsafe.Pointer(cr))
+	defer C.free(unsafe.Pointer(cs))
+	var ev C.accel_event
+	var comp C.int
+	buf := (*C.char)(C.malloc(2048))
+	defer C.free(unsafe.Pointer(buf))
+	err = locked(func() C.int { return C.accel_tfjob_local_action(cj, cr, C.int(firstSpecType), C.int(activePods),
+		C.int(succeeded), cs, &ev, &comp, buf, 2048) })
+	if err != nil {
+		return
+	}
+	return int(ev.action), int(ev.number), comp != 0, C.GoString(buf), nil
 }

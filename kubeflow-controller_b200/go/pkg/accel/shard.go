@@ -198,3 +198,13 @@ func (c *Context) ApplyDevState(task, optimizer int, v, slot0, slot1 DevPtr, gra
 		C.uint64_t(count), &ch, (*C.float)(unsafe.Pointer(uintptr(sumsq))),
 		unsafe.Pointer(uintptr(devState)), C.accel_stream_t(unsafe.Pointer(stream))) })
 }
+
+// SetStepShape tunes the one-kernel step: reducerPct = share of CTAs that reduce + apply + pull in
+// the in-switch form (0 = default), coop = cooperative launch (false: plain launch for small grids).
+func (c *Context) SetStepShape(reducerPct int, coop bool) error {
+	k := C.int(0)
+	if coop {
+		k = 1
+	}
+	return locked(func() C.int { return C.accel_ctx_set_step_shape(c.h, C.int(reducerPct), k) })
+}

@@ -105,3 +105,21 @@ def test_bf16_rounding_is_nearest_even(x):
     want = torch.from_numpy(a).to(torch.bfloat16).view(torch.int16).numpy().view(np.uint16)
     finite = np.isfinite(O.bf16_bits_to_f32(want))
     assert np.array_equal(bits[finite], want[finite])
+
+
+@settings(max_examples=100, deadline=None)
+@given(sizes=st.lists(st.integers(1, 10**6), min_size=1, max_size=80), world=st.integers(1, 16),
+       first=st.integers(0, 20))
+def test_bucket_layout_invariants(pkg, sizes, world, first):
+    """Round-robin buckets as equal shards of the multi-GPU arena: every variable lies wholly in
+    the shard of its round-robin task, nothing overlaps, the arena is `world` equal shards."""
+    from kubeflow_controller_b200.sharded import BucketLayout
+    lay = BucketLayout(sizes, world, first_task=first)
+    assert lay.arena == lay.shard * world and lay.shard % 8 == 0 and lay.shard >= max(lay.fill)
+    spans = sorted((lay.pos[k], lay.pos[k] + sizes[k]) for k in range(len(sizes)))
+    assert all(a[1] <= b[0] for a, b in zip(spans, spans[1:]))
+    for k, n in enumerate(sizes):
+        t = (first + k) % world
+        assert lay.task[k] == t
+        assert lay.pos[k] // lay.shard == t == (lay.pos[k] + n - 1) // lay.shard
+        assert lay.pos[k] % 8 == 0
