@@ -558,7 +558,8 @@ int accel_shard_reset(accel_ctx *ctx, const accel_peers *peers, accel_stream_t s
 
 /* Share of the one-kernel step's CTAs that reduce + apply + pull under
  * ACCEL_OVERLAP_SWITCH (percent, 1..90; 0 restores the default: 25 with one
- * local gradient, 8 with several).
+ * local gradient, 8 with several), or that apply + pull under
+ * ACCEL_OVERLAP_ROLES (default 50: every second CTA).
  * coop = 1 (default) launches the one-kernel step cooperatively (co-residency
  * guaranteed or the launch fails); coop = 0 uses a plain launch when the grid
  * is at most one CTA per SM — lower launch latency for small shards, safe only

@@ -218,9 +218,23 @@ __global__ void __launch_bounds__(kFusedThreads, 2)
 
   if (fa.roles && nb > 1) {
     // ---- split roles: pushers never stop to apply, appliers trail them by one slice --------
-    const int n_push = (nb + 1) / 2, n_apply = nb / 2;
-    const int rb = bid >> 1;
-    if ((bid & 1) == 0) {
+    // applier share in percent (fa.roles): 50 = every second CTA (the original split); any other
+    // value puts the first n_apply CTAs on apply + pull and the rest on push
+    int n_apply, rb;
+    bool pusher;
+    if (fa.roles == 50) {
+      n_apply = nb / 2;
+      rb = bid >> 1;
+      pusher = (bid & 1) == 0;
+    } else {
+      n_apply = nb * fa.roles / 100;
+      if (n_apply < 1) n_apply = 1;
+      if (n_apply > nb - 1) n_apply = nb - 1;
+      pusher = bid >= n_apply;
+      rb = pusher ? bid - n_apply : bid;
+    }
+    const int n_push = nb - n_apply;
+    if (pusher) {
       // Pusher. The per-slice ticket is taken per WARP (no CTA barrier): a warp that has
       // finished its part of slice k fences its own stores and moves on to slice k+1 while the
       // other warps keep the memory system busy.
@@ -362,6 +376,9 @@ static int check_switch(const ShardArgs &a) {
 // (the link probe is flat from 74 CTAs up and slower at 37). With several local gradients the
 // HBM-bound summers need the CTAs: 8 % (6-12 % within noise of each other at 8 GPUs, 25 % slower,
 // 3 % starves the links; profiles/r02_sharded_step.md).
+// ACCEL_OVERLAP_ROLES: share of the CTAs that apply + pull (the rest push), in percent.
+static int roles_percent(const Tuning &t) { return t.reducer_pct > 0 ? t.reducer_pct : 50; }
+
 static int reducer_percent(const Tuning &t, int n_workers) {
   if (t.reducer_pct > 0) return t.reducer_pct;
   return n_workers == 1 ? 25 : 8;
@@ -383,7 +400,7 @@ int accel_shard_step_fused(accel_ctx *ctx, const accel_peers *peers, int optimiz
                  grad_sumsq_dev, &fa.r[0]);
   if (rc) return rc;
   fa.n_slices = clamp_slices(n_slices, peers->shard_elems);
-  fa.roles = overlap == ACCEL_OVERLAP_ROLES;
+  fa.roles = overlap == ACCEL_OVERLAP_ROLES ? roles_percent(ctx->tuning) : 0;
   fa.n_reducers = reducer_percent(ctx->tuning, n_workers);   // percent; the launcher turns it into CTAs
   fa.trace = ctx->tuning.trace;
   fa.l2hint = ctx->tuning.l2hint;
@@ -443,7 +460,7 @@ int accel_shard_step_local_group(accel_ctx *ctx, const accel_peers *const *peers
                   "a local group has no NVSwitch between its ranks: multicast pointers must be NULL");
   }
   fa.n_slices = clamp_slices(n_slices, peers_of_rank[0]->shard_elems);
-  fa.roles = overlap == ACCEL_OVERLAP_ROLES;
+  fa.roles = overlap == ACCEL_OVERLAP_ROLES ? roles_percent(ctx->tuning) : 0;
   fa.n_reducers = reducer_percent(ctx->tuning, n_workers);
   fa.trace = 0;
   fa.l2hint = 0;

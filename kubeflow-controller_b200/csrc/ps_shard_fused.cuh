@@ -19,7 +19,7 @@ struct FusedArgs {
   ShardArgs r[R];
   int ctas_per_rank;
   int n_slices;
-  int roles;  // ACCEL_OVERLAP_ROLES: even CTAs only push, odd CTAs only apply+pull
+  int roles;  // ACCEL_OVERLAP_ROLES: percent of the CTAs that only apply + pull (0 = every CTA does both)
   int n_reducers;  // ACCEL_OVERLAP_SWITCH: CTAs per rank that reduce + apply + pull; the rest sum
   int trace;       // development: stamp %globaltimer into flag words [128, 256)
   int l2hint;      // development: L2 evict-first gradient loads / evict-last stage stores (summers)

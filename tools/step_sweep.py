@@ -78,6 +78,24 @@ def main():
         del grads
         torch.cuda.empty_cache()
 
+    if "roles" in what:
+        # unicast step with split roles: share of the CTAs that apply + pull (the rest push)
+        padded = -(-ELEMS // (8 * world)) * 8 * world
+        grads = [torch.randn(padded, device=dev) * 0.01 for _ in range(WORKERS)]
+        for slices, pct in ((4, 50), (4, 40), (4, 30), (4, 25), (4, 20), (4, 15), (8, 30), (8, 25),
+                            (8, 20), (2, 25), (16, 25)):
+            sps = ShardedPS(rank, world, local, ELEMS, pkg.OPT_SGD, pkg.HParams(lr=0.01),
+                            mode="fused", n_chunks=slices, overlap=1)
+            sps.ctx.set_step_shape(pct, True)
+            ms = timed(lambda: sps.step(grads, stream), 20, 4, stream, dev)
+            sps.check(stream)
+            emit({"case": "headline, unicast step, split roles", "world": world, "slices": slices,
+                  "applier_pct": pct, "ms": round(ms, 4)})
+            del sps
+            torch.cuda.empty_cache()
+        del grads
+        torch.cuda.empty_cache()
+
     if "tune" in what:
         # second pass over the in-switch step: reducer share x quads in flight x slices
         padded = -(-ELEMS // (8 * world)) * 8 * world
